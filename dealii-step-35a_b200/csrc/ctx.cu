@@ -1,0 +1,422 @@
+#include "ctx.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+
+namespace s35 {
+
+namespace {
+
+// greedy colouring on shared DoFs, used when the caller passes no colouring
+std::vector<int32_t> color_cells_by_dofs(int32_t n_cells, int dpc, int32_t n_dofs, const int32_t *cell_dofs)
+{
+  std::vector<int32_t> ptr(n_dofs + 1, 0);
+  for (size_t k = 0; k < (size_t)n_cells * dpc; ++k)
+    ptr[cell_dofs[k] + 1]++;
+  for (int32_t i = 0; i < n_dofs; ++i)
+    ptr[i + 1] += ptr[i];
+  std::vector<int32_t> cells((size_t)n_cells * dpc), fill(ptr.begin(), ptr.end() - 1);
+  for (int32_t c = 0; c < n_cells; ++c)
+    for (int i = 0; i < dpc; ++i)
+      cells[fill[cell_dofs[(size_t)c * dpc + i]]++] = c;
+  std::vector<int32_t> color(n_cells, -1);
+  for (int32_t c = 0; c < n_cells; ++c)
+    {
+      uint64_t used = 0;
+      for (int i = 0; i < dpc; ++i)
+        {
+          const int32_t d = cell_dofs[(size_t)c * dpc + i];
+          for (int32_t k = ptr[d]; k < ptr[d + 1]; ++k)
+            if (color[cells[k]] >= 0)
+              used |= 1ull << color[cells[k]];
+        }
+      int col = 0;
+      while (used & (1ull << col))
+        ++col;
+      S35_REQUIRE(col < 63, "cell colouring needs more than 63 colours");
+      color[c] = col;
+    }
+  return color;
+}
+
+} // namespace
+
+Ctx::Ctx(const s35_problem &p)
+{
+  S35_REQUIRE(p.dim == 2 || p.dim == 3, "problem: dim must be 2 or 3");
+  S35_REQUIRE(p.n_cells > 0 && p.n_vel > 0 && p.n_pres > 0, "problem: empty mesh");
+  S35_REQUIRE(p.cell_vertices && p.vel_cell_dofs, "problem: null geometry arrays");
+  S35_REQUIRE(p.velc_rowptr && p.velc_col && p.velm_rowptr && p.velm_col && p.velm_val, "problem: null velocity matrices");
+  S35_REQUIRE(p.grad_rowptr && p.grad_col && p.plap_rowptr && p.plap_col && p.plap_val && p.pmass_rowptr && p.pmass_col &&
+                p.pmass_val,
+              "problem: null pressure matrices");
+  S35_REQUIRE(p.dt > 0 && p.reynolds > 0, "problem: dt and Reynolds must be positive");
+  S35_REQUIRE(p.vel_max_iterations >= 1 && p.vel_update_prec >= 1, "problem: bad solver parameters");
+  if (p.vel_off_diagonals != 0)
+    throw Error(S35_ERR_UNSUPPORTED, "off_diagonals > 0 (banded ILU pattern augmentation) is not part of this build; "
+                                     "use off_diagonals = 0 as parameter-file.prm does");
+  dim = p.dim;
+  n_cells = p.n_cells;
+  nv = p.n_vel;
+  np = p.n_pres;
+  dt = p.dt;
+  reynolds = p.reynolds;
+  eps = p.vel_eps;
+  diag_strength = p.vel_diag_strength;
+  max_its = p.vel_max_iterations;
+  krylov = p.vel_krylov_size;
+  update_prec = p.vel_update_prec;
+  rotational = p.rotational != 0;
+  if (const char *t = std::getenv("S35_TIMERS"))
+    timers_enabled = std::atoi(t) != 0;
+
+  S35_CUDA(cudaGetDevice(&device));
+  S35_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  cudaStream_t s = stream;
+
+  vel_adv.create(nv, nv, p.velc_rowptr, p.velc_col, nullptr, s);
+  vel_mass.create(nv, nv, p.velm_rowptr, p.velm_col, p.velm_val, s);
+  S35_REQUIRE(p.grad_val[0] != nullptr, "problem: null gradient operator");
+  grad.create(nv, np, p.grad_rowptr, p.grad_col, p.grad_val[0], s);
+  gradT = &grad.transpose(s);
+  for (int d = 0; d < dim; ++d)
+    {
+      S35_REQUIRE(p.grad_val[d] != nullptr, "problem: null gradient operator");
+      it_val[d].alloc(vel_adv.nnz);
+      grad_val[d].upload(p.grad_val[d], grad.nnz, s);
+      gradT_val[d].alloc(grad.nnz);
+      gather_values(gradT_val[d], grad_val[d], grad.transposed->perm, grad.nnz, s);
+    }
+  plap.create(np, np, p.plap_rowptr, p.plap_col, p.plap_val, s);
+  pmass.create(np, np, p.pmass_rowptr, p.pmass_col, p.pmass_val, s);
+  {
+    std::vector<double> inv(np);
+    for (int32_t r = 0; r < np; ++r)
+      {
+        int32_t pos = -1;
+        for (int32_t k = p.pmass_rowptr[r]; k < p.pmass_rowptr[r + 1]; ++k)
+          if (p.pmass_col[k] == r)
+            pos = k;
+        S35_REQUIRE(pos >= 0 && p.pmass_val[pos] != 0.0, "problem: pres_Mass lacks a diagonal entry");
+        inv[r] = 1.0 / p.pmass_val[pos];
+      }
+    pmass_inv_diag.upload(inv, s);
+  }
+
+  // constraints
+  std::vector<char> wall_mask(nv, 0);
+  for (int32_t i = 0; i < p.n_wall; ++i)
+    {
+      S35_REQUIRE(p.wall_dofs[i] >= 0 && p.wall_dofs[i] < nv, "problem: wall DoF out of range");
+      wall_mask[p.wall_dofs[i]] = 1;
+    }
+  n_wall = p.n_wall;
+  wall_dofs.upload(p.wall_dofs, p.n_wall, s);
+  n_proj = p.n_proj;
+  for (int32_t i = 0; i < p.n_proj; ++i)
+    S35_REQUIRE(p.proj_dofs[i] >= 0 && p.proj_dofs[i] < np, "problem: projection DoF out of range");
+  proj_dofs.upload(p.proj_dofs, p.n_proj, s);
+  for (int d = 0; d < dim; ++d)
+    flow[d].create(vel_adv, p.n_flow[d], p.flow_dofs[d], p.flow_vals[d], s);
+
+  // assembly
+  const int dpc = dim == 3 ? 27 : 9;
+  std::vector<int32_t> own_colors;
+  const int32_t *colors = p.cell_color;
+  if (!colors)
+    {
+      own_colors = color_cells_by_dofs(n_cells, dpc, nv, p.vel_cell_dofs);
+      colors = own_colors.data();
+    }
+  assembler.create(dim, n_cells, p.cell_vertices, p.vel_cell_dofs, colors, vel_adv, wall_mask, s);
+  {
+    // number of distinct vertices, for the algorithmic byte count: Q2 corner nodes of all cells
+    std::vector<char> seen(nv, 0);
+    const int corner_idx3[8] = {0, 2, 6, 8, 18, 20, 24, 26}, corner_idx2[4] = {0, 2, 6, 8};
+    for (int32_t c = 0; c < n_cells; ++c)
+      for (int v = 0; v < (1 << dim); ++v)
+        seen[p.vel_cell_dofs[(size_t)c * dpc + (dim == 3 ? corner_idx3[v] : corner_idx2[v])]] = 1;
+    n_vertices = std::count(seen.begin(), seen.end(), (char)1);
+  }
+
+  // preconditioners (pressure: built once, step-35a.cc:1070-1074) and solvers
+  for (int d = 0; d < dim; ++d)
+    prec_vel[d].create(vel_adv, s);
+  prec_pres.create(plap, s);
+  prec_pres.factor(plap.val, diag_strength, s);
+  prec_pres.check_pivots(s);
+  gmres.init(nv, krylov, s);
+  cg.init(np, s);
+  ws.init(s);
+  scal.alloc(8);
+  scal.zero(s);
+  scal_host.alloc(8);
+
+  for (int d = 0; d < dim; ++d)
+    {
+      for (DevBuf<double> *v : {&u_n[d], &u_nm1[d], &u_star[d], &force[d], &v_tmp[d]})
+        {
+          v->alloc(nv);
+          v->zero(s);
+        }
+    }
+  for (DevBuf<double> *v : {&pres_n, &pres_nm1, &phi_n, &phi_nm1, &pres_tmp, &p_work})
+    {
+      v->alloc(np);
+      v->zero(s);
+    }
+  S35_CUDA(cudaStreamSynchronize(s));
+}
+
+Ctx::~Ctx()
+{
+  for (auto &pd : pending)
+    {
+      cudaEventDestroy(pd.a);
+      cudaEventDestroy(pd.b);
+    }
+  for (auto e : event_pool)
+    cudaEventDestroy(e);
+  if (stream)
+    cudaStreamDestroy(stream);
+}
+
+size_t Ctx::begin_section(const char *name)
+{
+  if (!timers_enabled)
+    return 0;
+  auto get_event = [&]() {
+    cudaEvent_t e;
+    if (!event_pool.empty())
+      {
+        e = event_pool.back();
+        event_pool.pop_back();
+      }
+    else
+      S35_CUDA(cudaEventCreate(&e));
+    return e;
+  };
+  Pending pd{name, get_event(), get_event()};
+  S35_CUDA(cudaEventRecord(pd.a, stream));
+  pending.push_back(pd);
+  return pending.size() - 1;
+}
+
+void Ctx::end_section(size_t id)
+{
+  if (!timers_enabled)
+    return;
+  S35_CUDA(cudaEventRecord(pending[id].b, stream));
+}
+
+void Ctx::resolve_sections()
+{
+  if (pending.empty())
+    return;
+  S35_CUDA(cudaStreamSynchronize(stream));
+  for (auto &pd : pending)
+    {
+      float ms = 0.f;
+      S35_CUDA(cudaEventElapsedTime(&ms, pd.a, pd.b));
+      SectionTimer &t = sections[pd.name];
+      t.ms += ms;
+      t.calls += 1;
+      event_pool.push_back(pd.a);
+      event_pool.push_back(pd.b);
+    }
+  pending.clear();
+}
+
+double *Ctx::field(s35_field f, int component, int64_t &len)
+{
+  const bool vel = f == S35_U_N || f == S35_U_N_MINUS_1 || f == S35_U_STAR || f == S35_FORCE;
+  if (vel)
+    S35_REQUIRE(component >= 0 && component < dim, "field: component out of range");
+  len = vel ? nv : np;
+  switch (f)
+    {
+    case S35_U_N: return u_n[component];
+    case S35_U_N_MINUS_1: return u_nm1[component];
+    case S35_U_STAR: return u_star[component];
+    case S35_FORCE: return force[component];
+    case S35_PRES_N: return pres_n;
+    case S35_PRES_N_MINUS_1: return pres_nm1;
+    case S35_PHI_N: return phi_n;
+    case S35_PHI_N_MINUS_1: return phi_nm1;
+    case S35_PRES_TMP: return pres_tmp;
+    }
+  throw Error(S35_ERR_INVALID, "field: unknown field id");
+}
+
+// step-35a.cc:1244-1254: u_star = 2 u_n - u_n_minus_1
+void Ctx::interpolate_velocity()
+{
+  const size_t sec = begin_section("interpolate_velocity");
+  for (int d = 0; d < dim; ++d)
+    vec_lincomb(u_star[d], DScal(2.0), u_n[d], DScal(-1.0), u_nm1[d], nv, stream);
+  end_section(sec);
+}
+
+// step-35a.cc:1346-1453
+void Ctx::assemble_advection_term()
+{
+  const size_t sec = begin_section("assemble_advection_term");
+  const double *us[3] = {u_star[0], u_star[1], u_star[2]};
+  assembler.assemble(vel_adv.val, vel_adv.nnz, us, dt, reynolds, stream);
+  vel_adv.values_changed();
+  end_section(sec);
+}
+
+// step-35a.cc:1268-1338
+void Ctx::diffusion_step(bool reinit_prec)
+{
+  cudaStream_t s = stream;
+  // pres_tmp = -pres_n - 4/3 phi_n + 1/3 phi_n_minus_1
+  vec_lincomb3(pres_tmp, DScal(-1.0), pres_n, DScal(-4.0 / 3.0), phi_n, DScal(1.0 / 3.0), phi_nm1, np, s);
+  {
+    const size_t sec = begin_section("setup_diffusion_rhs");
+    for (int d = 0; d < dim; ++d)
+      {
+        vec_lincomb(v_tmp[d], DScal(2.0 / dt), u_n[d], DScal(-0.5 / dt), u_nm1[d], nv, s);
+        spmv(vel_mass, v_tmp[d], force[d], false, s);                       // force = 0 + vel_Mass v_tmp
+        spmv_values(grad, grad_val[d], pres_tmp, force[d], true, s);        // force += pres_Diff[d] pres_tmp
+        vec_copy(u_nm1[d], u_n[d], nv, s);
+        vec_copy(it_val[d], vel_adv.val, vel_adv.nnz, s);                   // vel_it_matrix[d].copy_from(vel_Advection)
+      }
+    end_section(sec);
+  }
+  {
+    const size_t sec = begin_section("solve_diffusion_component");
+    diag_abs_mean(vel_adv, vel_adv.val, scal.ptr + 0, ws, s);
+    for (int d = 0; d < dim; ++d)
+      {
+        flow[d].condense(vel_adv, it_val[d], force[d], scal.ptr + 0, s);
+        if (reinit_prec)
+          {
+            prec_vel[d].factor(it_val[d], diag_strength, s);
+            prec_vel[d].check_pivots(s);
+          }
+        vec_dot(scal.ptr + 1 + d, force[d], force[d], nv, kSqrt, ws, s);
+        S35_CUDA(cudaMemcpyAsync(scal_host.ptr + 1 + d, scal.ptr + 1 + d, sizeof(double), cudaMemcpyDeviceToHost, s));
+        S35_CUDA(cudaStreamSynchronize(s));
+        const double tol = eps * scal_host.ptr[1 + d];
+        const bool ok = gmres.solve(vel_adv, it_val[d], prec_vel[d], u_n[d], force[d], tol, max_its, stats_vel[d]);
+        if (!ok)
+          {
+            end_section(sec);
+            resolve_sections();
+            throw Error(S35_ERR_NO_CONVERGENCE, "GMRES did not converge for velocity component " + std::to_string(d) +
+                                                  " after " + std::to_string(stats_vel[d].iterations) + " iterations, residual " +
+                                                  std::to_string(stats_vel[d].final_residual));
+          }
+        vec_scatter_set(u_n[d], flow[d].dofs, flow[d].values, flow[d].n_constrained, s); // flow constraints distribute
+        vec_scatter_set(u_n[d], wall_dofs, nullptr, n_wall, s);                          // wall constraints distribute
+      }
+    end_section(sec);
+  }
+}
+
+// step-35a.cc:1456-1508 (#else branch)
+void Ctx::projection_step()
+{
+  cudaStream_t s = stream;
+  {
+    const size_t sec = begin_section("projection_step_setup");
+    const double *vals[3] = {gradT_val[0], gradT_val[1], gradT_val[2]};
+    const double *xs[3] = {u_n[0], u_n[1], u_n[2]};
+    spmv_multi(*gradT, dim, vals, xs, pres_tmp, false, s); // pres_tmp = sum_d pres_Diff[d]^T u_n[d]
+    vec_copy(phi_nm1, phi_n, np, s);
+    end_section(sec);
+  }
+  {
+    const size_t sec = begin_section("projection_step_solve");
+    vec_dot(scal.ptr + 4, pres_tmp, pres_tmp, np, kSqrt, ws, s); // the tolerance uses the norm before condense
+    S35_CUDA(cudaMemcpyAsync(scal_host.ptr + 4, scal.ptr + 4, sizeof(double), cudaMemcpyDeviceToHost, s));
+    vec_scatter_set(pres_tmp, proj_dofs, nullptr, n_proj, s); // projection_constraints.condense(pres_tmp)
+    S35_CUDA(cudaStreamSynchronize(s));
+    const double tol = eps * scal_host.ptr[4];
+    const bool ok = cg.solve(plap, plap.val, &prec_pres, phi_n, pres_tmp, tol, max_its, stats_proj);
+    if (!ok)
+      {
+        end_section(sec);
+        resolve_sections();
+        throw Error(S35_ERR_NO_CONVERGENCE, "CG did not converge in the projection step after " +
+                                              std::to_string(stats_proj.iterations) + " iterations, residual " +
+                                              std::to_string(stats_proj.final_residual));
+      }
+    vec_scatter_set(phi_n, proj_dofs, nullptr, n_proj, s); // projection_constraints.distribute(phi_n)
+    end_section(sec);
+  }
+  {
+    const size_t sec = begin_section("projection_step_setup");
+    vec_lincomb(phi_n, DScal(1.5 / dt), phi_n, DScal(0.0), nullptr, np, s);
+    end_section(sec);
+  }
+}
+
+// step-35a.cc:1511-1545 (#else branch).  The reference's UMFPACK solve with pres_Mass is replaced by
+// Jacobi-preconditioned CG run to 1e-14 relative: the Q1 mass matrix is SPD and well conditioned.
+void Ctx::update_pressure()
+{
+  cudaStream_t s = stream;
+  const size_t sec = begin_section("update_pressure");
+  vec_copy(pres_nm1, pres_n, np, s);
+  if (!rotational)
+    vec_lincomb(pres_n, DScal(1.0), pres_n, DScal(1.0), phi_n, np, s);
+  else
+    {
+      vec_dot(scal.ptr + 5, pres_tmp, pres_tmp, np, kSqrt, ws, s);
+      S35_CUDA(cudaMemcpyAsync(scal_host.ptr + 5, scal.ptr + 5, sizeof(double), cudaMemcpyDeviceToHost, s));
+      p_work.zero(s);
+      S35_CUDA(cudaStreamSynchronize(s));
+      const double tol = 1e-14 * scal_host.ptr[5];
+      // a stagnating residual recurrence near machine precision is not a failure of the time step
+      cg.solve(pmass, pmass.val, nullptr, p_work, pres_tmp, tol, 200, stats_mass, pmass_inv_diag);
+      // pres_n = 1/Re * M^-1 pres_tmp + pres_n_minus_1 + phi_n
+      vec_lincomb3(pres_n, DScal(1.0 / reynolds), p_work, DScal(1.0), pres_nm1, DScal(1.0), phi_n, np, s);
+    }
+  end_section(sec);
+}
+
+// the body of the loop in run(), step-35a.cc:1190-1239
+void Ctx::advance(int first_n, int n_steps, int start_n, int start_offset_n, double *elapsed_ms)
+{
+  cudaEvent_t e0, e1;
+  S35_CUDA(cudaEventCreate(&e0));
+  S35_CUDA(cudaEventCreate(&e1));
+  S35_CUDA(cudaEventRecord(e0, stream));
+  try
+    {
+      for (int n = first_n; n < first_n + n_steps; ++n)
+        {
+          if (n == start_offset_n)
+            {
+              interpolate_velocity();
+              assemble_advection_term();
+            }
+          diffusion_step((n % update_prec == 0) || (n == start_n));
+          interpolate_velocity();
+          assemble_advection_term();
+          projection_step();
+          update_pressure();
+          resolve_sections();
+        }
+    }
+  catch (...)
+    {
+      cudaEventDestroy(e0);
+      cudaEventDestroy(e1);
+      throw;
+    }
+  S35_CUDA(cudaEventRecord(e1, stream));
+  S35_CUDA(cudaEventSynchronize(e1));
+  float ms = 0.f;
+  S35_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  if (elapsed_ms)
+    *elapsed_ms = ms;
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+}
+
+} // namespace s35

@@ -1,0 +1,91 @@
+// Device context of one NavierStokesProjection object: every matrix, vector,
+// constraint list and preconditioner the time loop touches
+// (step-35a.cc:474-520), resident in HBM between steps.
+#pragma once
+#include "assembly.cuh"
+#include "krylov.cuh"
+
+#include <map>
+#include <string>
+
+namespace s35 {
+
+struct SectionTimer
+{
+  double ms = 0.0;
+  int64_t calls = 0;
+};
+
+struct Ctx
+{
+  int dim = 0;
+  int32_t n_cells = 0, nv = 0, np = 0;
+  int64_t n_vertices = 0;
+  double dt = 0, reynolds = 0, eps = 0, diag_strength = 0;
+  int max_its = 0, krylov = 0, update_prec = 0;
+  bool rotational = true;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+
+  // matrices
+  DevMatrix vel_adv;              // constrained pattern; values = vel_Advection
+  DevBuf<double> it_val[3];       // vel_it_matrix[d] values on the same pattern
+  DevMatrix vel_mass;             // unconstrained pattern
+  DevMatrix grad;                 // pres_Diff pattern; values of component 0
+  DevBuf<double> grad_val[3];     // pres_Diff[d] values
+  const DevMatrix *gradT = nullptr; // transposed pattern (owned by grad)
+  DevBuf<double> gradT_val[3];
+  DevMatrix plap, pmass;
+  DevBuf<double> pmass_inv_diag;
+
+  // constraints
+  CondensePlan flow[3];
+  DevBuf<int32_t> wall_dofs, proj_dofs;
+  int32_t n_wall = 0, n_proj = 0;
+
+  // preconditioners and solvers
+  DevIlu prec_vel[3], prec_pres;
+  GmresSolver gmres;
+  CgSolver cg;
+  AdvectionAssembler assembler;
+  ReduceWs ws;
+  DevBuf<double> scal; // [0] mean |diag|, [1..3] ||force_d||, [4] ||pres_tmp||
+  PinnedBuf<double> scal_host;
+
+  // vectors
+  DevBuf<double> u_n[3], u_nm1[3], u_star[3], force[3], v_tmp[3];
+  DevBuf<double> pres_n, pres_nm1, phi_n, phi_nm1, pres_tmp, p_work;
+
+  s35_solver_stats stats_vel[3] = {}, stats_proj = {}, stats_mass = {};
+  std::map<std::string, SectionTimer> sections;
+  bool timers_enabled = true;
+
+  // open timer sections of the current call: (name, start, stop)
+  struct Pending
+  {
+    std::string name;
+    cudaEvent_t a, b;
+  };
+  std::vector<Pending> pending;
+  std::vector<cudaEvent_t> event_pool;
+
+  explicit Ctx(const s35_problem &p);
+  ~Ctx();
+  Ctx(const Ctx &) = delete;
+  Ctx &operator=(const Ctx &) = delete;
+
+  void interpolate_velocity();
+  void assemble_advection_term();
+  void diffusion_step(bool reinit_prec);
+  void projection_step();
+  void update_pressure();
+  void advance(int first_n, int n_steps, int start_n, int start_offset_n, double *elapsed_ms);
+
+  double *field(s35_field f, int component, int64_t &len);
+
+  size_t begin_section(const char *name);
+  void end_section(size_t id);
+  void resolve_sections();
+};
+
+} // namespace s35

@@ -1,0 +1,43 @@
+// ILU(0) on the device: deal.II SparseILU<double>::initialize (Saad's IKJ
+// variant, in place, inverse pivots on the diagonal) and ::vmult (forward
+// substitution with the unit lower factor, backward substitution with the
+// upper factor) -- step-35a.cc:1070-1074, 1312-1319 and the preconditioner
+// calls inside SolverGMRES / SolverCG.  SURVEY.md Appendix A.3.
+//
+// The factors are exactly those of the reference's elimination order; only the
+// schedule differs.  Both phases are "sync-free": rows are handed out in a
+// topological order (dependency level, then row index) through a ticket
+// counter, and a row waits for the rows it depends on.
+//  * factorisation: one warp per row, a ready flag per row;
+//  * substitution: G lanes per row; the solution vector itself is the flag --
+//    it is pre-filled with a NaN bit pattern no arithmetic produces, and a
+//    consumer polls the entry it needs (through L2) until it changes.
+#pragma once
+#include "sparse.cuh"
+
+namespace s35 {
+
+struct DevIlu
+{
+  const DevMatrix *pattern = nullptr; // not owned; must outlive this object
+  int32_t n = 0;
+  DevBuf<double> lu;                  // factor values on the pattern of A
+  DevBuf<int32_t> order_fwd, order_bwd;
+  DevBuf<double> y;                   // forward-substitution result, kept armed with the sentinel
+  DevBuf<int32_t> ready;              // factorisation: row finished
+  DevBuf<int32_t> tickets;            // [0] forward, [1] backward, [2] factor, [3] zero-pivot flag
+  int32_t levels_fwd = 0, levels_bwd = 0;
+  int group = 8;                      // lanes per row in the substitutions
+  bool factored = false;
+
+  void create(const DevMatrix &A, cudaStream_t s);
+  // lu = values (+ strengthen * sum|offdiag| on the diagonal), then factorise
+  void factor(const double *values, double strengthen_diagonal, cudaStream_t s);
+  // throws S35_ERR_ZERO_PIVOT if the last factorisation met a zero pivot (synchronises the stream)
+  void check_pivots(cudaStream_t s);
+  // dst = (LU)^-1 src; dst must not alias src
+  void apply(double *dst, const double *src, cudaStream_t s);
+  double apply_bytes() const { return 12.0 * pattern->nnz + 4.0 * (n + 1.0) + 4.0 * n + 32.0 * n; }
+};
+
+} // namespace s35

@@ -1,0 +1,223 @@
+#include "krylov.cuh"
+
+#include <cmath>
+#include <limits>
+
+namespace s35 {
+
+void GmresSolver::init(int32_t n_, int krylov_size, cudaStream_t s)
+{
+  S35_REQUIRE(krylov_size >= 3, "GMRES: Krylov_size must be at least 3 (two of the vectors are work space)");
+  S35_REQUIRE(krylov_size <= 34, "GMRES: Krylov_size above 34 is not supported by this build");
+  n = n_;
+  n_tmp = krylov_size;
+  stride = ((int64_t)n + 1) & ~(int64_t)1;
+  tmp.alloc((size_t)stride * n_tmp);
+  h_dev.alloc(n_tmp + 4);
+  h_host.alloc(n_tmp + 4);
+  ws.init(s);
+  stream = s;
+}
+
+bool GmresSolver::solve(const DevMatrix &P, const double *values, DevIlu &prec, double *x, const double *b, double tol,
+                        int max_iterations, s35_solver_stats &stats)
+{
+  cudaStream_t s = stream;
+  auto vec = [&](int i) { return tmp.ptr + (size_t)i * stride; };
+  double *const v = vec(0), *const p = vec(n_tmp - 1);
+  double *const hd = h_dev.ptr;
+  double *const hh = h_host.ptr;
+  const int i_norm = n_tmp, i_start = n_tmp + 1; // slots for ||vv|| and ||vv||_start
+
+  std::vector<double> H((size_t)n_tmp * (n_tmp - 1), 0.0); // H(i,j) = H[i*(n_tmp-1)+j]
+  std::vector<double> gamma(n_tmp), ci(n_tmp - 1), si(n_tmp - 1), h(n_tmp - 1);
+  auto Hm = [&](int i, int j) -> double & { return H[(size_t)i * (n_tmp - 1) + j]; };
+
+  int accumulated = 0;
+  unsigned dim = 0;
+  SolverState state = SolverState::iterate;
+  double last_res = -std::numeric_limits<double>::max();
+  bool reorthogonalize = false;
+  stats.initial_residual = 0.0;
+  stats.tolerance = tol;
+
+  do
+    {
+      std::fill(h.begin(), h.end(), 0.0);
+      // p = b - A x ; v = P^-1 p
+      spmv_values(P, values, x, p, false, s);
+      vec_lincomb(p, DScal(-1.0), p, DScal(1.0), b, n, s);
+      prec.apply(v, p, s);
+      vec_dot(hd + i_norm, v, v, n, kSqrt, ws, s);
+      S35_CUDA(cudaMemcpyAsync(hh + i_norm, hd + i_norm, sizeof(double), cudaMemcpyDeviceToHost, s));
+      S35_CUDA(cudaStreamSynchronize(s));
+      double rho = hh[i_norm];
+      if (accumulated == 0)
+        stats.initial_residual = rho;
+      last_res = rho;
+      state = solver_check(accumulated, rho, tol, max_iterations);
+      if (state != SolverState::iterate)
+        break;
+      gamma[0] = rho;
+      vec_lincomb(v, DScal(1.0 / rho), v, DScal(0.0), nullptr, n, s);
+
+      for (int inner = 0; inner < n_tmp - 2 && state == SolverState::iterate; ++inner)
+        {
+          ++accumulated;
+          double *vv = vec(inner + 1);
+          spmv_values(P, values, vec(inner), p, false, s);
+          prec.apply(vv, p, s);
+          dim = inner + 1;
+
+          // modified Gram-Schmidt (SolverGMRES::modified_gram_schmidt)
+          const bool consider_reorthogonalize = !reorthogonalize && (inner % 5 == 4);
+          if (consider_reorthogonalize)
+            vec_dot(hd + i_start, vv, vv, n, kSqrt, ws, s);
+          vec_dot(hd + 0, vv, vec(0), n, kSum, ws, s);
+          for (unsigned i = 1; i < dim; ++i)
+            vec_add_and_dot(hd + i, vv, DScal(hd + i - 1, -1.0), vec(i - 1), vec(i), n, kSum, ws, s);
+          vec_add_and_dot(hd + i_norm, vv, DScal(hd + dim - 1, -1.0), vec(dim - 1), vv, n, kSqrt, ws, s);
+          S35_CUDA(cudaMemcpyAsync(hh, hd, (n_tmp + 2) * sizeof(double), cudaMemcpyDeviceToHost, s));
+          S35_CUDA(cudaStreamSynchronize(s));
+          for (unsigned i = 0; i < dim; ++i)
+            h[i] = hh[i];
+          double norm_vv = hh[i_norm];
+          if (consider_reorthogonalize)
+            {
+              const double norm_vv_start = hh[i_start];
+              if (!(norm_vv > 10. * norm_vv_start * std::sqrt(std::numeric_limits<double>::epsilon())))
+                reorthogonalize = true;
+            }
+          if (reorthogonalize)
+            {
+              // second pass, entered once loss of orthogonality has been detected; corrections add to h
+              vec_dot(hd + 0, vv, vec(0), n, kSum, ws, s);
+              for (unsigned i = 1; i < dim; ++i)
+                vec_add_and_dot(hd + i, vv, DScal(hd + i - 1, -1.0), vec(i - 1), vec(i), n, kSum, ws, s);
+              vec_add_and_dot(hd + i_norm, vv, DScal(hd + dim - 1, -1.0), vec(dim - 1), vv, n, kSqrt, ws, s);
+              S35_CUDA(cudaMemcpyAsync(hh, hd, (n_tmp + 2) * sizeof(double), cudaMemcpyDeviceToHost, s));
+              S35_CUDA(cudaStreamSynchronize(s));
+              for (unsigned i = 0; i < dim; ++i)
+                h[i] += hh[i];
+              norm_vv = hh[i_norm];
+            }
+          const double sn = norm_vv;
+          h[inner + 1] = sn;
+          // s = 0 is a lucky breakdown; do not divide by zero
+          if (std::isfinite(1. / sn))
+            vec_lincomb(vv, DScal(1. / sn), vv, DScal(0.0), nullptr, n, s);
+
+          // SolverGMRES::givens_rotation
+          for (int i = 0; i < inner; ++i)
+            {
+              const double sg = si[i], cg = ci[i], dummy = h[i];
+              h[i] = cg * dummy + sg * h[i + 1];
+              h[i + 1] = -sg * dummy + cg * h[i + 1];
+            }
+          const double r = 1. / std::sqrt(h[inner] * h[inner] + h[inner + 1] * h[inner + 1]);
+          si[inner] = h[inner + 1] * r;
+          ci[inner] = h[inner] * r;
+          h[inner] = ci[inner] * h[inner] + si[inner] * h[inner + 1];
+          gamma[inner + 1] = -si[inner] * gamma[inner];
+          gamma[inner] *= ci[inner];
+
+          for (unsigned i = 0; i < dim; ++i)
+            Hm(i, inner) = h[i];
+          rho = std::fabs(gamma[dim]);
+          last_res = rho;
+          state = solver_check(accumulated, rho, tol, max_iterations);
+        }
+      // back substitution H1 y = gamma (FullMatrix::backward), then x += sum y_i v_i
+      std::vector<double> y(dim);
+      for (int i = (int)dim - 1; i >= 0; --i)
+        {
+          double sum = gamma[i];
+          for (unsigned j = i + 1; j < dim; ++j)
+            sum -= Hm(i, j) * y[j];
+          y[i] = sum / Hm(i, i);
+        }
+      vec_multi_axpy(x, vec(0), stride, y.data(), (int)dim, n, s);
+    }
+  while (state == SolverState::iterate);
+
+  stats.iterations = accumulated;
+  stats.final_residual = last_res;
+  return state == SolverState::success;
+}
+
+void CgSolver::init(int32_t n_, cudaStream_t s)
+{
+  n = n_;
+  g.alloc(n);
+  d.alloc(n);
+  h.alloc(n);
+  scal.alloc(8);
+  res_host.alloc(2);
+  ws.init(s);
+  stream = s;
+}
+
+bool CgSolver::solve(const DevMatrix &P, const double *values, DevIlu *prec, double *x, const double *b, double tol,
+                     int max_iterations, s35_solver_stats &stats, const double *inv_diag)
+{
+  cudaStream_t s = stream;
+  double *const sc = scal.ptr;
+  enum
+  {
+    DH = 0,
+    ALPHA = 1,
+    GH = 2,
+    RES = 3,
+    GHNEW = 4,
+    BETA = 5
+  };
+  auto read_res = [&]() {
+    S35_CUDA(cudaMemcpyAsync(res_host.ptr, sc + RES, sizeof(double), cudaMemcpyDeviceToHost, s));
+    S35_CUDA(cudaStreamSynchronize(s));
+    return res_host.ptr[0];
+  };
+  auto precondition = [&](double *dst, const double *src) {
+    if (prec)
+      prec->apply(dst, src, s);
+    else if (inv_diag)
+      vec_multiply(dst, inv_diag, src, n, s);
+    else
+      vec_copy(dst, src, n, s);
+  };
+  stats.tolerance = tol;
+  int it = 0;
+  // g = A x - b (for x == 0 this is exactly -b, the reference's short cut)
+  spmv_values(P, values, x, g, false, s);
+  vec_add_and_dot(sc + RES, g, DScal(-1.0), b, g, n, kSqrt, ws, s);
+  double res = read_res();
+  stats.initial_residual = res;
+  SolverState state = solver_check(0, res, tol, max_iterations);
+  if (state == SolverState::iterate)
+    {
+      precondition(h, g);
+      vec_lincomb(d, DScal(-1.0), h, DScal(0.0), nullptr, n, s);
+      vec_dot(sc + GH, g, h, n, kSum, ws, s);
+      while (state == SolverState::iterate)
+        {
+          ++it;
+          spmv_values(P, values, d, h, false, s);
+          vec_dot(sc + DH, d, h, n, kSum, ws, s);
+          scalar_divide(sc + ALPHA, sc + GH, sc + DH, nullptr, s);
+          vec_cg_update(sc + RES, x, g, DScal(sc + ALPHA), d, h, n, ws, s);
+          res = read_res();
+          state = solver_check(it, res, tol, max_iterations);
+          if (state != SolverState::iterate)
+            break;
+          precondition(h, g);
+          vec_dot(sc + GHNEW, g, h, n, kSum, ws, s);
+          // beta = gh_new / gh_old ; gh = gh_new
+          scalar_divide(sc + BETA, sc + GHNEW, sc + GH, sc + GH, s);
+          vec_lincomb(d, DScal(sc + BETA), d, DScal(-1.0), h, n, s);
+        }
+    }
+  stats.iterations = it;
+  stats.final_residual = res;
+  return state == SolverState::success;
+}
+
+} // namespace s35

@@ -1,0 +1,61 @@
+// Device Krylov solvers that follow deal.II's SolverGMRES / SolverCG step by
+// step (call sites step-35a.cc:1334-1337 and
+// 1496-1499), so that they stop at the same iterate as the reference.
+// Vectors live on the device; the Hessenberg / Givens bookkeeping of GMRES
+// (a handful of scalars per iteration) is done on the host exactly as
+// deal.II does it, after one read-back per iteration.
+#pragma once
+#include "ilu.cuh"
+#include "vecops.cuh"
+
+namespace s35 {
+
+// SolverControl::check
+enum class SolverState
+{
+  iterate,
+  success,
+  failure
+};
+inline SolverState solver_check(int step, double value, double tol, int max_steps)
+{
+  if (value <= tol)
+    return SolverState::success;
+  if (step >= max_steps || value != value)
+    return SolverState::failure;
+  return SolverState::iterate;
+}
+
+struct GmresSolver
+{
+  int32_t n = 0;
+  int n_tmp = 0;          // AdditionalData::max_n_tmp_vectors (= Krylov_size)
+  int64_t stride = 0;     // distance between basis vectors
+  DevBuf<double> tmp;     // n_tmp vectors
+  DevBuf<double> h_dev;   // MGS coefficients + norms
+  PinnedBuf<double> h_host;
+  ReduceWs ws;
+  cudaStream_t stream = 0;
+
+  void init(int32_t n, int krylov_size, cudaStream_t s);
+  // returns false on SolverControl failure (iteration limit / NaN); x holds the last iterate either way
+  bool solve(const DevMatrix &pattern, const double *values, DevIlu &prec, double *x, const double *b, double tol,
+             int max_iterations, s35_solver_stats &stats);
+};
+
+struct CgSolver
+{
+  int32_t n = 0;
+  DevBuf<double> g, d, h;
+  DevBuf<double> scal;    // [0] d.h  [1] alpha  [2] gh  [3] res  [4] gh_new  [5] beta
+  PinnedBuf<double> res_host;
+  ReduceWs ws;
+  cudaStream_t stream = 0;
+
+  void init(int32_t n, cudaStream_t s);
+  // prec may be null; then inv_diag (Jacobi, h = inv_diag .* g) is used if given, else PreconditionIdentity
+  bool solve(const DevMatrix &pattern, const double *values, DevIlu *prec, double *x, const double *b, double tol,
+             int max_iterations, s35_solver_stats &stats, const double *inv_diag = nullptr);
+};
+
+} // namespace s35

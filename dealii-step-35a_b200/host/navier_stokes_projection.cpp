@@ -1,0 +1,347 @@
+#include "navier_stokes_projection.h"
+
+#include "h5lite.h"
+
+#include <chrono>
+#include <cstdio>
+#include <iomanip>
+#include <iostream>
+#include <sstream>
+#include <stdexcept>
+
+namespace Step35 {
+
+ProblemView::ProblemView(const s35::Discretization &D, const RunTimeParameters::Data_Storage &data)
+{
+  const int dim = D.dim, vpc = 1 << dim;
+  const int64_t n_cells = D.mesh.n_cells();
+  cell_vertices.resize((size_t)n_cells * vpc * dim);
+  for (int64_t c = 0; c < n_cells; ++c)
+    for (int v = 0; v < vpc; ++v)
+      for (int k = 0; k < dim; ++k)
+        cell_vertices[((size_t)c * vpc + v) * dim + k] = D.mesh.vertices[(size_t)D.mesh.cells[c * vpc + v] * dim + k];
+  s35_problem &p = problem;
+  p = s35_problem{};
+  p.dim = dim;
+  p.n_cells = (int32_t)n_cells;
+  p.n_vel = D.vel.n_dofs;
+  p.n_pres = D.pres.n_dofs;
+  p.cell_vertices = cell_vertices.data();
+  p.vel_cell_dofs = D.vel.cell_dofs.data();
+  p.cell_color = D.cell_color.data();
+  p.velc_rowptr = D.vel_pattern_constrained.rowptr.data();
+  p.velc_col = D.vel_pattern_constrained.col.data();
+  p.velm_rowptr = D.vel_pattern_unconstrained.rowptr.data();
+  p.velm_col = D.vel_pattern_unconstrained.col.data();
+  p.velm_val = D.vel_mass.data();
+  p.grad_rowptr = D.grad_pattern.rowptr.data();
+  p.grad_col = D.grad_pattern.col.data();
+  for (int d = 0; d < dim; ++d)
+    p.grad_val[d] = D.pres_diff[d].data();
+  p.plap_rowptr = D.proj_pattern.rowptr.data();
+  p.plap_col = D.proj_pattern.col.data();
+  p.plap_val = D.pres_laplace.data();
+  p.pmass_rowptr = D.pres_pattern.rowptr.data();
+  p.pmass_col = D.pres_pattern.col.data();
+  p.pmass_val = D.pres_mass.data();
+  p.n_wall = (int32_t)D.wall_dofs.size();
+  p.wall_dofs = D.wall_dofs.data();
+  for (int d = 0; d < dim; ++d)
+    {
+      p.n_flow[d] = (int32_t)D.flow_dofs[d].size();
+      p.flow_dofs[d] = D.flow_dofs[d].data();
+      p.flow_vals[d] = D.flow_vals[d].data();
+    }
+  p.n_proj = (int32_t)D.proj_dofs.size();
+  p.proj_dofs = D.proj_dofs.data();
+  p.dt = data.dt;
+  p.reynolds = data.Reynolds;
+  p.vel_eps = data.vel_eps;
+  p.vel_diag_strength = data.vel_diag_strength;
+  p.vel_max_iterations = (int32_t)data.vel_max_iterations;
+  p.vel_krylov_size = (int32_t)data.vel_Krylov_size;
+  p.vel_off_diagonals = (int32_t)data.vel_off_diagonals;
+  p.vel_update_prec = (int32_t)data.vel_update_prec;
+  p.rotational = data.form == RunTimeParameters::METHOD_ROTATIONAL ? 1 : 0;
+}
+
+template <int dim>
+void NavierStokesProjection<dim>::check(s35_status st)
+{
+  if (st != S35_OK)
+    throw std::runtime_error(s35_last_error());
+}
+
+template <int dim>
+NavierStokesProjection<dim>::NavierStokesProjection(const RunTimeParameters::Data_Storage &data, const std::string &mesh_file)
+  : type(data.form), deg(data.pressure_degree), dt(data.dt), t_0(data.initial_time), T(data.final_time), Re(data.Reynolds),
+    load_checkpoint_file_name(data.load_checkpoint_file_name), save_checkpoint_file_name(data.save_checkpoint_file_name),
+    vel_max_its(data.vel_max_iterations), vel_Krylov_size(data.vel_Krylov_size), vel_off_diagonals(data.vel_off_diagonals),
+    vel_update_prec(data.vel_update_prec), vel_eps(data.vel_eps), vel_diag_strength(data.vel_diag_strength), parameters(data)
+{
+  if (deg < 1)
+    std::cout << " WARNING: The chosen pair of finite element spaces is not stable." << std::endl
+              << " The obtained results will be nonsense" << std::endl;
+  // AssertThrow at step-35a.cc:731
+  if ((dt <= 0.) || (dt > .5 * T))
+    {
+      std::ostringstream msg;
+      msg << " The time step " << dt << " is out of range." << std::endl << " The permitted range is (0," << .5 * T << "]";
+      throw std::runtime_error(msg.str());
+    }
+  create_triangulation_and_dofs(data.n_global_refines, mesh_file);
+  initialize();
+}
+
+template <int dim>
+NavierStokesProjection<dim>::~NavierStokesProjection()
+{
+  s35_ctx_destroy(ctx);
+}
+
+template <int dim>
+void NavierStokesProjection<dim>::create_triangulation_and_dofs(const unsigned int n_refines, const std::string &mesh_file)
+{
+  const auto t0 = std::chrono::steady_clock::now();
+  const std::string filename = !mesh_file.empty() ? mesh_file : (dim == 3 ? "cylinderextruded.msh" : "nsbench2.inp");
+  s35::Mesh coarse = s35::read_mesh(filename, dim);
+  std::cout << "Number of refines = " << n_refines << '\n';
+  s35::DiscretizationOptions opt;
+  opt.n_refines = (int)n_refines;
+  opt.pressure_degree = (int)deg;
+  opt.dt = dt;
+  disc = s35::build_discretization(coarse, opt);
+  std::cout << "minimum cell diameter: " << s35::minimal_cell_diameter(disc->mesh) << '\n';
+  std::cout << "Number of active cells: " << disc->mesh.n_cells() << std::endl;
+  width = disc->width;
+  height = disc->height;
+  std::cout << "width: " << width << std::endl;
+  std::cout << "height: " << height << std::endl;
+
+  view.reset(new ProblemView(*disc, parameters));
+  check(s35_ctx_create(&view->problem, &ctx));
+
+  std::cout << "dim (X_h) = " << ((long)disc->vel.n_dofs * dim) << std::endl
+            << "dim (M_h) = " << disc->pres.n_dofs << std::endl
+            << "Re        = " << Re << std::endl
+            << std::endl;
+  setup_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+// step-35a.cc:834-854: p = 25 - x at both time levels, phi = 0, u = 0
+template <int dim>
+void NavierStokesProjection<dim>::initialize()
+{
+  std::vector<double> zero_v(disc->vel.n_dofs, 0.0), zero_p(disc->pres.n_dofs, 0.0);
+  check(s35_ctx_set_field(ctx, S35_PRES_N_MINUS_1, 0, disc->pres_nm1_0.data()));
+  check(s35_ctx_set_field(ctx, S35_PRES_N, 0, disc->pres_n0.data()));
+  check(s35_ctx_set_field(ctx, S35_PHI_N, 0, zero_p.data()));
+  check(s35_ctx_set_field(ctx, S35_PHI_N_MINUS_1, 0, zero_p.data()));
+  for (int d = 0; d < dim; ++d)
+    {
+      check(s35_ctx_set_field(ctx, S35_U_N_MINUS_1, d, zero_v.data()));
+      check(s35_ctx_set_field(ctx, S35_U_N, d, zero_v.data()));
+    }
+}
+
+template <int dim>
+void NavierStokesProjection<dim>::load_checkpoint()
+{
+  if (load_checkpoint_file_name.size() == 0)
+    return;
+  std::vector<double> v;
+  for (int block_n = 0; block_n < dim; ++block_n)
+    {
+      H5::load(load_checkpoint_file_name, "u_n" + std::to_string(block_n), v);
+      check(s35_ctx_set_field(ctx, S35_U_N, block_n, v.data()));
+      H5::load(load_checkpoint_file_name, "u_n_minus_1" + std::to_string(block_n), v);
+      check(s35_ctx_set_field(ctx, S35_U_N_MINUS_1, block_n, v.data()));
+    }
+  H5::load(load_checkpoint_file_name, "phi_n", v);
+  check(s35_ctx_set_field(ctx, S35_PHI_N, 0, v.data()));
+  H5::load(load_checkpoint_file_name, "phi_n_minus_1", v);
+  check(s35_ctx_set_field(ctx, S35_PHI_N_MINUS_1, 0, v.data()));
+  H5::load(load_checkpoint_file_name, "pres_n", v);
+  check(s35_ctx_set_field(ctx, S35_PRES_N, 0, v.data()));
+  H5::load(load_checkpoint_file_name, "pres_n_minus_1", v);
+  check(s35_ctx_set_field(ctx, S35_PRES_N_MINUS_1, 0, v.data()));
+}
+
+template <int dim>
+void NavierStokesProjection<dim>::save_checkpoint()
+{
+  if (save_checkpoint_file_name.size() == 0)
+    return;
+  const std::string file = output_directory + "/" + save_checkpoint_file_name;
+  std::cout << "outfile name is '" << save_checkpoint_file_name << "'" << std::endl;
+  std::remove(file.c_str());
+  std::vector<double> v(disc->vel.n_dofs), p(disc->pres.n_dofs);
+  for (int block_n = 0; block_n < dim; ++block_n)
+    {
+      check(s35_ctx_get_field(ctx, S35_U_N, block_n, v.data()));
+      H5::save(file, "u_n" + std::to_string(block_n), v);
+      check(s35_ctx_get_field(ctx, S35_U_N_MINUS_1, block_n, v.data()));
+      H5::save(file, "u_n_minus_1" + std::to_string(block_n), v);
+    }
+  check(s35_ctx_get_field(ctx, S35_PHI_N, 0, p.data()));
+  H5::save(file, "phi_n", p);
+  check(s35_ctx_get_field(ctx, S35_PHI_N_MINUS_1, 0, p.data()));
+  H5::save(file, "phi_n_minus_1", p);
+  check(s35_ctx_get_field(ctx, S35_PRES_N, 0, p.data()));
+  H5::save(file, "pres_n", p);
+  check(s35_ctx_get_field(ctx, S35_PRES_N_MINUS_1, 0, p.data()));
+  H5::save(file, "pres_n_minus_1", p);
+}
+
+template <int dim>
+unsigned int NavierStokesProjection<dim>::n_time_steps() const
+{
+  // step-35a.cc:1174,1190-1191: n runs from 2 to n_steps on a fresh start
+  const unsigned int n_steps = static_cast<unsigned int>((T - t_0) / dt);
+  return load_checkpoint_file_name.empty() ? (n_steps >= 1 ? n_steps - 1 : 0) : n_steps + 1;
+}
+
+template <int dim>
+void NavierStokesProjection<dim>::run(const bool verbose, const unsigned int output_interval)
+{
+  auto verbose_cout = [&](const char *msg) {
+    if (verbose)
+      std::cout << msg << std::endl;
+  };
+  const unsigned int n_steps = static_cast<unsigned int>((T - t_0) / dt);
+  unsigned int step_start_n = 2;
+  unsigned int step_start_offset_n = 2;
+  if (load_checkpoint_file_name.size() == 0)
+    output_results(1, t_0);
+  else
+    {
+      load_checkpoint();
+      step_start_n = static_cast<unsigned int>(t_0 / dt);
+      step_start_offset_n = 0;
+    }
+  for (unsigned int n = step_start_n; n <= step_start_n + n_steps - step_start_offset_n; ++n)
+    {
+      const double current_time = (t_0 + (n - step_start_n + step_start_offset_n) * dt);
+      if (n % output_interval == 0)
+        {
+          verbose_cout("Plotting Solution");
+          output_results(n, current_time);
+        }
+      std::cout << "Step = " << n << " Time = " << current_time << std::endl;
+      verbose_cout("  Interpolating the velocity ");
+      // both of these are needed to do the diffusion step
+      if (n == step_start_offset_n)
+        {
+          interpolate_velocity();
+          assemble_advection_term();
+        }
+      verbose_cout("  Diffusion Step");
+      if (n % vel_update_prec == 0)
+        verbose_cout("    With reinitialization of the preconditioner");
+      diffusion_step((n % vel_update_prec == 0) || (n == step_start_n));
+      interpolate_velocity();
+      // the reference runs these two as concurrent tasks (step-35a.cc:1219-1235)
+      assemble_advection_term();
+      verbose_cout("  Projection Step");
+      projection_step();
+      verbose_cout("  Updating the Pressure");
+      update_pressure();
+      if (verbose)
+        {
+          s35_solver_stats st;
+          for (int d = 0; d < dim; ++d)
+            {
+              check(s35_ctx_solver_stats(ctx, d, &st));
+              std::cout << "    GMRES[" << d << "]: " << st.iterations << " iterations, residual " << st.final_residual << std::endl;
+            }
+          check(s35_ctx_solver_stats(ctx, -1, &st));
+          std::cout << "    CG: " << st.iterations << " iterations, residual " << st.final_residual << std::endl;
+        }
+    }
+  save_checkpoint();
+  print_timer_summary();
+}
+
+template <int dim>
+void NavierStokesProjection<dim>::interpolate_velocity()
+{
+  check(s35_interpolate_velocity(ctx));
+}
+template <int dim>
+void NavierStokesProjection<dim>::diffusion_step(const bool reinit_prec)
+{
+  check(s35_diffusion_step(ctx, reinit_prec ? 1 : 0));
+}
+template <int dim>
+void NavierStokesProjection<dim>::projection_step()
+{
+  check(s35_projection_step(ctx));
+}
+template <int dim>
+void NavierStokesProjection<dim>::update_pressure()
+{
+  check(s35_update_pressure(ctx));
+}
+template <int dim>
+void NavierStokesProjection<dim>::assemble_advection_term()
+{
+  check(s35_assemble_advection_term(ctx));
+}
+
+// The reference writes mesh.h5 / solution-%09d.h5 / solution.xdmf through deal.II's DataOut and a
+// snapshot-%09d.h5 of u_n (step-35a.cc:1548-1661).  Here the fields go into solution-%09d.h5 and
+// snapshot-%09d.h5 in the container of h5lite.h, datasets "v0".."v{dim-1}", "p" and "a0".."a{dim-1}".
+template <int dim>
+void NavierStokesProjection<dim>::output_results(const unsigned int step, const double time)
+{
+  (void)time;
+  char name[64];
+  std::snprintf(name, sizeof(name), "solution-%09u.h5", step);
+  const std::string sol = output_directory + "/" + name;
+  std::snprintf(name, sizeof(name), "snapshot-%09u.h5", step);
+  const std::string snap = output_directory + "/" + name;
+  std::remove(sol.c_str());
+  std::remove(snap.c_str());
+  std::vector<double> v(disc->vel.n_dofs), p(disc->pres.n_dofs);
+  for (int d = 0; d < dim; ++d)
+    {
+      check(s35_ctx_get_field(ctx, S35_U_N, d, v.data()));
+      H5::save(sol, "v" + std::to_string(d), v);
+      H5::save(snap, "a" + std::to_string(d), v);
+    }
+  check(s35_ctx_get_field(ctx, S35_PRES_N, 0, p.data()));
+  H5::save(sol, "p", p);
+}
+
+// TimerOutput summary (step-35a.cc:508,714): device time per section
+template <int dim>
+void NavierStokesProjection<dim>::print_timer_summary() const
+{
+  static const char *names[] = {"assemble_advection_term", "interpolate_velocity",     "projection_step_setup", "projection_step_solve",
+                                "setup_diffusion_rhs",     "solve_diffusion_component", "update_pressure"};
+  double total = 0.0;
+  double ms[7];
+  int64_t calls[7];
+  for (int i = 0; i < 7; ++i)
+    {
+      s35_ctx_section_ms(ctx, names[i], &ms[i], &calls[i]);
+      total += ms[i];
+    }
+  std::cout << "\n+---------------------------------------------+------------+------------+\n"
+            << "| Total device time elapsed in sections       |" << std::setw(10) << std::fixed << std::setprecision(3)
+            << total * 1e-3 << "s |            |\n"
+            << "| Section                         | no. calls  |  dev time  | % of total |\n"
+            << "+---------------------------------+------------+------------+------------+\n";
+  for (int i = 0; i < 7; ++i)
+    std::cout << "| " << std::left << std::setw(32) << names[i] << "|" << std::right << std::setw(11) << calls[i] << " |"
+              << std::setw(10) << std::setprecision(3) << ms[i] * 1e-3 << "s |" << std::setw(10) << std::setprecision(1)
+              << (total > 0 ? 100.0 * ms[i] / total : 0.0) << "% |\n";
+  std::cout << "+---------------------------------+------------+------------+------------+\n" << std::endl;
+  std::cout.unsetf(std::ios::fixed);
+  std::cout << std::setprecision(6);
+}
+
+template class NavierStokesProjection<2>;
+template class NavierStokesProjection<3>;
+
+} // namespace Step35
