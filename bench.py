@@ -1,0 +1,325 @@
+#!/usr/bin/env python
+"""Benchmark of the step-35a time-step path on B200.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--mesh M --dim D --refines R]
+
+One "step" is one pass of the loop body of NavierStokesProjection::run (step-35a.cc:1190-1239): diffusion step
+(per-component ILU(0)-GMRES), velocity extrapolation, advection assembly, projection step (ILU(0)-CG) and
+pressure update, on the 3D cylinder mesh (Q2/Q1, parameter-file.prm values with pressure_fe_degree = 1).
+Rank 0 prints ONE JSON line.  `--impl reference` times the CPU oracle (the reference itself needs deal.II and
+cannot be built here) on the host cores with the same workload, metric and unit.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import __graft_entry__ as ge  # noqa: E402
+
+REYNOLDS = {"cylinderextruded": 100.0, "cylinder3d": 20.0, "nsbench2": 100.0}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--mesh", default="cylinderextruded")
+    ap.add_argument("--dim", type=int, default=3)
+    ap.add_argument("--refines", type=int, default=1)
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-kernels", action="store_true", help="skip the per-kernel roofline pass")
+    return ap.parse_args()
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons while the timed region runs."""
+
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index):
+        self.device_index = device_index
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device_index), "--query-gpu=" + self.QUERY,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smax.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def workload_name(args):
+    return "%s r%d %dD Q2/Q1 Re=%g" % (args.mesh, args.refines, args.dim, REYNOLDS.get(args.mesh, 100.0))
+
+
+def build_disc(pkg, args):
+    params = pkg.default_params(reynolds=REYNOLDS.get(args.mesh, 100.0), final_time=1.0, dt=5e-4, vel_eps=1e-8,
+                                vel_off_diagonals=0, vel_diag_strength=0.0, vel_update_prec=100, vel_krylov_size=30,
+                                vel_max_iterations=1000, n_global_refines=args.refines, pressure_degree=1, rotational=1)
+    mesh_file = os.path.join(ROOT, "meshes", args.mesh + ".s35m")
+    return pkg.Disc(mesh_file, args.dim, params), params
+
+
+def iteration_counts(c, dim):
+    return {"gmres": [c.solver_stats(d).iterations for d in range(dim)], "cg": c.solver_stats(-1).iterations}
+
+
+def cpu_arm(pkg, disc, args, budget_seconds, steps=None, warmup=0):
+    """The oracle (-O3 -march=native, OpenMP over cells / components / rows like the reference's TBB use) on
+    the host cores.  Returns steps/s over a bounded sample."""
+    import oracle_binding as ob
+
+    cores = os.cpu_count() or 1
+    orc = ob.Oracle(disc.problem, fast=True, threads=cores)
+    orc.set_field(pkg.PRES_N, disc.initial_pressure)
+    orc.set_field(pkg.PRES_N_MINUS_1, disc.initial_pressure)
+    n = 2
+    for _ in range(warmup):
+        orc.advance(n, 1)
+        n += 1
+    done, t0 = 0, time.perf_counter()
+    while True:
+        orc.advance(n, 1)
+        n += 1
+        done += 1
+        elapsed = time.perf_counter() - t0
+        if steps is not None:
+            if done >= steps:
+                break
+        elif elapsed >= budget_seconds or done >= 50:
+            break
+    sections = {s: orc.section_seconds(s) for s in pkg.SECTIONS}
+    its = iteration_counts(orc, disc.dim)
+    orc.close()
+    return done / elapsed, cores, done, sections, its
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    pkg = ge.load_package()
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        disc, _ = build_disc(pkg, args)
+        dof = disc.dim * disc.nv + disc.np_
+        rate, cores, done, sections, its = cpu_arm(pkg, disc, args, args.cpu_seconds, steps=args.steps, warmup=args.warmup)
+        line = {
+            "impl": "reference", "metric": "time_steps_per_s", "value": rate, "unit": "steps/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / rate, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(args), "dof": dof, "n_vel_per_component": disc.nv, "n_pres": disc.np_},
+            "dof_steps_per_s": rate * dof, "iterations": its,
+            "cpu_baseline": {"value": rate, "unit": "steps/s", "cores": cores, "kind": "port",
+                             "sample": "%d warm-up + %d timed steps of the same workload; oracle/oracle.cpp built -O3 "
+                                       "-march=native with OpenMP (the reference needs deal.II: unavailable on this box)"
+                                       % (args.warmup, done)},
+            "e2e": {"value": rate, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "sections_s": sections,
+        }
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+
+    if pkg.device_count() < 1:
+        raise RuntimeError("bench.py: no CUDA device; the device path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    pkg.check(pkg.lib().s35_set_device(local_rank))
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    disc, params = build_disc(pkg, args)
+    dim, nv, np_ = disc.dim, disc.nv, disc.np_
+    dof = dim * nv + np_
+    t0 = time.perf_counter()
+    ctx = pkg.Ctx(disc.problem)
+    ctx_seconds = time.perf_counter() - t0
+    ctx.set_field(pkg.PRES_N, disc.initial_pressure)
+    ctx.set_field(pkg.PRES_N_MINUS_1, disc.initial_pressure)
+
+    # ---- device-resident run: W warm-up steps, then exactly K timed steps
+    n = 2
+    if args.warmup:
+        ctx.advance(n, args.warmup)
+        n += args.warmup
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    launches0 = pkg.launch_count()
+    sec0 = {s: ctx.section_ms(s)[0] for s in pkg.SECTIONS}
+    t0 = time.perf_counter()
+    dev_ms = ctx.advance(n, args.steps)
+    barrier()
+    wall_s = time.perf_counter() - t0
+    launches = pkg.launch_count() - launches0
+    clocks = sampler.stop()
+    n += args.steps
+    its = iteration_counts(ctx, dim)
+    sections = {s: (ctx.section_ms(s)[0] - sec0[s]) / args.steps for s in pkg.SECTIONS}
+    elapsed = max(dev_ms * 1e-3, 0.0)
+    t = torch.tensor([elapsed, wall_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    elapsed, wall_s = float(t[0]), float(t[1])
+    # every rank advances its own replica of the workload ("replicas only")
+    value = world * args.steps / elapsed
+
+    # ---- end to end through the C ABI with host buffers: the state a host-side caller owns (the checkpoint set of
+    # step-35a.cc:865-875) goes to the device from pinned memory every step and comes back after it
+    e2e = None
+    fields_v = (pkg.U_N, pkg.U_N_MINUS_1)
+    fields_p = (pkg.PRES_N, pkg.PRES_N_MINUS_1, pkg.PHI_N, pkg.PHI_N_MINUS_1)
+    host = {}
+    for f in fields_v:
+        for d in range(dim):
+            buf = torch.empty(nv, dtype=torch.float64, pin_memory=True).numpy()
+            buf[:] = ctx.get_field(f, d)
+            host[(f, d)] = buf
+    for f in fields_p:
+        buf = torch.empty(np_, dtype=torch.float64, pin_memory=True).numpy()
+        buf[:] = ctx.get_field(f)
+        host[(f, 0)] = buf
+    lib = pkg.lib()
+
+    def e2e_step(step_n):
+        for (f, d), buf in host.items():
+            pkg.check(lib.s35_ctx_set_field(ctx.handle, f, d, pkg.dptr(buf)))
+        ctx.advance(step_n, 1, start_n=-1, start_offset_n=-1)
+        for (f, d), buf in host.items():
+            pkg.check(lib.s35_ctx_get_field(ctx.handle, f, d, pkg.dptr(buf)))
+
+    e2e_steps = max(1, min(args.steps, 5))
+    e2e_step(n)
+    n += 1
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step(n)
+        n += 1
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    state_bytes = 8 * (len(fields_v) * dim * nv + len(fields_p) * np_)
+    e2e = {"value": world * e2e_steps / float(t[0]), "unit": "steps/s", "h2d_bytes_per_step": state_bytes,
+           "d2h_bytes_per_step": state_bytes, "steps": e2e_steps}
+
+    # ---- per-kernel rooflines (CUDA events on the launch stream, L2 flushed between launches)
+    peak, peak_kind = load_peaks()
+    kernels = {}
+    if not args.no_kernels:
+        names = {"spmv_vel": pkg.BENCH_SPMV_VEL, "spmv_pres": pkg.BENCH_SPMV_PRES, "spmv_grad": pkg.BENCH_SPMV_GRAD,
+                 "spmv_grad_T": pkg.BENCH_SPMV_GRAD_T, "assemble_advection": pkg.BENCH_ASSEMBLE,
+                 "ilu_apply_vel": pkg.BENCH_ILU_APPLY_VEL, "ilu_apply_pres": pkg.BENCH_ILU_APPLY_PRES,
+                 "dot": pkg.BENCH_DOT, "add_and_dot": pkg.BENCH_ADD_AND_DOT}
+        for name, kid in names.items():
+            ms, nbytes, nl = ctx.bench_kernel(kid, warmup=3, reps=10, flush_l2=True)
+            gbs = nbytes / (ms * 1e-3) / 1e9
+            kernels[name] = {"ms": ms, "algorithmic_bytes": nbytes, "GB/s": gbs, "frac": gbs / peak, "launches": nl}
+    # the kernel that dominates the step: the ILU(0) substitution sweeps (SpMV is reported beside it)
+    roofline = None
+    if kernels:
+        per_step = {
+            "ilu_apply_vel": kernels["ilu_apply_vel"]["ms"] * (sum(its["gmres"]) + dim),
+            "ilu_apply_pres": kernels["ilu_apply_pres"]["ms"] * (its["cg"] + 1),
+            "spmv_vel": kernels["spmv_vel"]["ms"] * (sum(its["gmres"]) + dim),
+            "assemble_advection": kernels["assemble_advection"]["ms"],
+        }
+        dominant = max(per_step, key=per_step.get)
+        k = kernels[dominant]
+        roofline = {"kernel": dominant, "bound": "hbm", "achieved": k["GB/s"], "peak": peak, "unit": "GB/s",
+                    "frac": k["frac"], "traffic": None, "peak_source": peak_kind,
+                    "share_of_step": per_step[dominant] / (1e3 * elapsed / args.steps),
+                    "note": "critical-path bound (dependency levels x L2 latency), not bandwidth bound: see DESIGN.md"
+                    if dominant.startswith("ilu") else ""}
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        rate, cores, done, cpu_sections, cpu_its = cpu_arm(pkg, disc, args, args.cpu_seconds)
+        cpu_baseline = {"value": rate, "unit": "steps/s", "cores": cores, "kind": "port",
+                        "sample": "%d time steps of the same workload from the same initial state (oracle/oracle.cpp, "
+                                  "-O3 -march=native, OpenMP)" % done,
+                        "sections_s_per_step": {k: v / done for k, v in cpu_sections.items()}, "iterations": cpu_its}
+
+    if rank == 0:
+        line = {
+            "metric": "time_steps_per_s", "value": value, "unit": "steps/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(args), "dof": dof, "n_vel_per_component": nv, "n_pres": np_,
+                       "cells": disc.n_cells, "parallelism": "replicas x%d" % world,
+                       "l2": "working set (%.0f MB of matrices) exceeds L2; kernel benchmarks flush L2 between launches"
+                             % ((disc.info.nnz_vel_constrained * (dim + 1) * 8 + disc.info.nnz_vel_constrained * 4) / 1e6)},
+            "dof_steps_per_s": value * dof, "iterations": its, "wall_ms_per_step": 1e3 * wall_s / args.steps,
+            "sections_ms_per_step": sections, "gpu_launches": launches, "clocks": clocks, "e2e": e2e, "roofline": roofline,
+            "kernels": kernels, "cpu_baseline": cpu_baseline,
+            "setup_s": {"host_discretisation": disc.info.setup_seconds, "device_context": ctx_seconds},
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,180 @@
+"""The time-step path on the device against the CPU oracle: one reference member function at a time, then
+whole steps.
+
+Field tolerance: 1e-8 relative to the field norm, in the maximum and in the l2 norm (BASELINE.json north
+star), wherever the problem itself is determined that well.  The Krylov solvers stop at eps * ||rhs||, so a
+field is only defined up to about eps * condition number: on the finer meshes two correct implementations
+differ by more than 1e-8 (tests/test_oracle.py shows the two independent CPU restatements differing by
+1e-7 in the pressure on nsbench2 r3, with eps = 1e-8 and with eps = 1e-12 alike).  Those cases carry their
+own, stated, tolerance."""
+import numpy as np
+import pytest
+
+from conftest import rel_diff, start_state
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-8
+
+
+def make_pair(pkg, ob, disc):
+    ctx, orc = pkg.Ctx(disc.problem), ob.Oracle(disc.problem)
+    start_state(pkg, disc, ctx, orc)
+    return ctx, orc
+
+
+def velocity_scale(orc, pkg, dim):
+    return max(np.abs(orc.get_field(pkg.U_N, d)).max() for d in range(dim))
+
+
+def assert_fields_match(pkg, ctx, orc, dim, tol=TOL):
+    """max-norm and l2-norm differences relative to the field norm (velocity: the norm of the whole vector field)."""
+    for f in (pkg.U_N, pkg.U_N_MINUS_1):
+        a = np.concatenate([ctx.get_field(f, d) for d in range(dim)])
+        b = np.concatenate([orc.get_field(f, d) for d in range(dim)])
+        assert rel_diff(a, b) < tol
+        assert np.linalg.norm(a - b) <= tol * np.linalg.norm(b)
+    for f in (pkg.PRES_N, pkg.PRES_N_MINUS_1, pkg.PHI_N, pkg.PHI_N_MINUS_1):
+        a, b = ctx.get_field(f), orc.get_field(f)
+        assert rel_diff(a, b) < tol
+        assert np.linalg.norm(a - b) <= tol * np.linalg.norm(b)
+
+
+@pytest.mark.parametrize("mesh,dim,refines", [("nsbench2.s35m", 2, 0), ("nsbench2.s35m", 2, 2), ("cylinder3d.s35m", 3, 0)])
+def test_each_member_function(pkg, ob, make_disc, mesh, dim, refines):
+    disc = make_disc(mesh, dim, n_global_refines=refines, reynolds=100.0 if dim == 2 else 20.0)
+    ctx, orc = make_pair(pkg, ob, disc)
+    nnz = int(disc.csr("velc")[0][-1])
+    # a non-trivial state: two oracle steps, copied to the device
+    orc.advance(2, 2)
+    for f in (pkg.U_N, pkg.U_N_MINUS_1, pkg.U_STAR):
+        for d in range(dim):
+            ctx.set_field(f, orc.get_field(f, d), d)
+    for f in (pkg.PRES_N, pkg.PRES_N_MINUS_1, pkg.PHI_N, pkg.PHI_N_MINUS_1):
+        ctx.set_field(f, orc.get_field(f))
+    scale = velocity_scale(orc, pkg, dim)
+
+    # interpolate_velocity
+    ctx.interpolate_velocity()
+    orc.interpolate_velocity()
+    for d in range(dim):
+        assert rel_diff(ctx.get_field(pkg.U_STAR, d), orc.get_field(pkg.U_STAR, d), scale) < 1e-15
+
+    # assemble_advection_term
+    ctx.assemble_advection_term()
+    orc.assemble_advection_term()
+    a_dev, a_ref = ctx.get_operator_values(pkg.VEL_ADVECTION, nnz), orc.get_operator_values(pkg.VEL_ADVECTION, nnz)
+    assert rel_diff(a_dev, a_ref) < 1e-12
+
+    # diffusion_step with a fresh preconditioner
+    ctx.diffusion_step(True)
+    orc.diffusion_step(True)
+    for d in range(dim):
+        m_dev, m_ref = ctx.get_operator_values(pkg.VEL_IT_MATRIX, nnz, d), orc.get_operator_values(pkg.VEL_IT_MATRIX, nnz, d)
+        assert rel_diff(m_dev, m_ref) < 1e-12
+        l_dev, l_ref = ctx.get_operator_values(pkg.VEL_ILU, nnz, d), orc.get_operator_values(pkg.VEL_ILU, nnz, d)
+        assert rel_diff(l_dev, l_ref) < 1e-11
+        assert rel_diff(ctx.get_field(pkg.FORCE, d), orc.get_field(pkg.FORCE, d)) < 1e-12
+        assert ctx.solver_stats(d).iterations == orc.solver_stats(d).iterations
+        assert rel_diff(ctx.get_field(pkg.U_N, d), orc.get_field(pkg.U_N, d), scale) < TOL
+
+    # projection_step
+    ctx.projection_step()
+    orc.projection_step()
+    assert rel_diff(ctx.get_field(pkg.PRES_TMP), orc.get_field(pkg.PRES_TMP)) < 1e-9
+    assert abs(ctx.solver_stats(-1).iterations - orc.solver_stats(-1).iterations) <= 1
+    assert rel_diff(ctx.get_field(pkg.PHI_N), orc.get_field(pkg.PHI_N)) < TOL
+
+    # update_pressure
+    ctx.update_pressure()
+    orc.update_pressure()
+    assert rel_diff(ctx.get_field(pkg.PRES_N), orc.get_field(pkg.PRES_N)) < TOL
+    assert_fields_match(pkg, ctx, orc, dim)
+
+
+@pytest.mark.parametrize("mesh,dim,refines,steps,reynolds,eps,tol",
+                         [("nsbench2.s35m", 2, 0, 20, 100.0, 1e-8, 1e-8),       # config 1 of BASELINE.json (first 20 steps)
+                          ("nsbench2.s35m", 2, 1, 10, 100.0, 1e-8, 1e-8),
+                          ("nsbench2.s35m", 2, 3, 6, 100.0, 1e-8, 2e-6),        # conditioning-limited, see module docstring
+                          ("nsbench2.s35m", 2, 3, 6, 100.0, 1e-12, 2e-6),
+                          ("cylinder3d.s35m", 3, 0, 3, 20.0, 1e-8, 1e-8)])      # config 3 of BASELINE.json (first steps)
+def test_time_steps_match_oracle(pkg, ob, make_disc, mesh, dim, refines, steps, reynolds, eps, tol):
+    disc = make_disc(mesh, dim, n_global_refines=refines, reynolds=reynolds, vel_eps=eps)
+    ctx, orc = make_pair(pkg, ob, disc)
+    ctx.advance(2, steps)
+    orc.advance(2, steps)
+    for d in range(dim):
+        assert abs(ctx.solver_stats(d).iterations - orc.solver_stats(d).iterations) <= 1
+    assert abs(ctx.solver_stats(-1).iterations - orc.solver_stats(-1).iterations) <= 0.05 * orc.solver_stats(-1).iterations + 1
+    assert_fields_match(pkg, ctx, orc, dim, tol)
+    u_dev = np.concatenate([ctx.get_field(pkg.U_N, d) for d in range(dim)])
+    u_ref = np.concatenate([orc.get_field(pkg.U_N, d) for d in range(dim)])
+    cd_dev = disc.drag_lift(reynolds, u_dev, ctx.get_field(pkg.PRES_N))
+    cd_ref = disc.drag_lift(reynolds, u_ref, orc.get_field(pkg.PRES_N))
+    assert np.abs(cd_dev - cd_ref).max() <= 1e-6 * max(1.0, np.abs(cd_ref).max())
+
+
+def test_standard_form_and_preconditioner_refresh(pkg, ob, make_disc):
+    disc = make_disc("nsbench2.s35m", 2, n_global_refines=1, rotational=0, vel_update_prec=3, vel_diag_strength=0.01)
+    ctx, orc = make_pair(pkg, ob, disc)
+    ctx.advance(2, 7)
+    orc.advance(2, 7)
+    assert_fields_match(pkg, ctx, orc, 2)
+
+
+def test_restart_path_uses_zero_advection_matrix(pkg, ob, make_disc):
+    # on a restart the reference never assembles before the first diffusion step (start_offset_n = 0)
+    disc = make_disc("nsbench2.s35m", 2, n_global_refines=1)
+    ctx, orc = make_pair(pkg, ob, disc)
+    ctx.advance(2, 3)
+    orc.advance(2, 3)
+    fields = {(f, d): orc.get_field(f, d) for f in (pkg.U_N, pkg.U_N_MINUS_1) for d in range(2)}
+    pf = {f: orc.get_field(f) for f in (pkg.PRES_N, pkg.PRES_N_MINUS_1, pkg.PHI_N, pkg.PHI_N_MINUS_1)}
+    ctx2, orc2 = pkg.Ctx(disc.problem), ob.Oracle(disc.problem)
+    for c in (ctx2, orc2):
+        for (f, d), v in fields.items():
+            c.set_field(f, v, d)
+        for f, v in pf.items():
+            c.set_field(f, v)
+    with pytest.raises(Exception):
+        # an all-zero vel_Advection makes the first factorisation hit a zero pivot in both implementations
+        orc2.advance(4, 1, start_n=4, start_offset_n=0)
+    with pytest.raises(pkg.S35Error):
+        ctx2.advance(4, 1, start_n=4, start_offset_n=0)
+
+
+def test_no_convergence_is_reported(pkg, make_disc):
+    disc = make_disc("nsbench2.s35m", 2, n_global_refines=2, vel_max_iterations=2)
+    ctx = pkg.Ctx(disc.problem)
+    start_state(pkg, disc, ctx)
+    with pytest.raises(pkg.S35Error) as e:
+        ctx.advance(2, 1)
+    assert e.value.status == 3
+
+
+def test_unsupported_off_diagonals(pkg, make_disc):
+    disc = make_disc("nsbench2.s35m", 2, vel_off_diagonals=5)
+    with pytest.raises(pkg.S35Error) as e:
+        pkg.Ctx(disc.problem)
+    assert e.value.status == 5
+
+
+def test_simulation_driver_runs_like_the_reference_loop(pkg, ob, make_disc, tmp_path):
+    import os
+    from conftest import MESH_DIR, run_params
+    params = run_params(pkg, n_global_refines=1, final_time=0.005)
+    sim = pkg.Simulation(params, os.path.join(MESH_DIR, "nsbench2.s35m"), 2)
+    assert sim.n_steps == 9  # (T - t0)/dt = 10, steps n = 2..10
+    cwd = os.getcwd()
+    os.chdir(tmp_path)
+    try:
+        sim.run(verbose=False, output_interval=999)
+    finally:
+        os.chdir(cwd)
+    orc = ob.Oracle(sim.disc.problem)
+    start_state(pkg, sim.disc, orc)
+    orc.advance(2, 9)
+    assert_fields_match(pkg, sim.ctx, orc, 2)
+    assert os.path.exists(tmp_path / "solution-000000001.h5")
+    ms, calls = sim.ctx.section_ms("projection_step_solve")
+    assert calls == 9 and ms > 0
