@@ -27,137 +27,108 @@ __device__ __forceinline__ double sentinel() { return __longlong_as_double(-1LL)
 // a NaN result must never look like the sentinel
 __device__ __forceinline__ double canonical(double v) { return v != v ? __longlong_as_double(0x7ff8000000000000LL) : v; }
 
-template <int G>
-__device__ __forceinline__ unsigned group_mask()
-{
-  if (G == 32)
-    return 0xffffffffu;
-  const int first = ((threadIdx.x & 31) / G) * G;
-  return ((1u << G) - 1u) << first;
-}
-
-// Forward substitution with the unit lower factor: y_r = src_r - sum_{c<r} L_rc y_c.
-// Also arms dst (the output of the backward sweep) with the sentinel.
-template <int G>
+// One substitution sweep, forward (unit lower factor: y_r = src_r - sum_{c<r} L_rc y_c) or backward
+// (x_r = (y_r - sum_{c>r} U_rc x_c) / u_rr, inverse pivot stored on the diagonal).
+//
+// One warp per row.  A lane first loads its (column, value) pairs of the row into registers -- P per lane
+// and chunk, all loads in flight together -- and only then polls the solution entries it needs, all pending
+// ones together and only the pending ones, so that rows far ahead of the wave front put one request per
+// unresolved dependency and polling round on L2, with a growing pause between rounds.  The wait for the
+// dependency that is produced last costs one round trip through L2 plus the warp reduction.  Every lane
+// adds its products in index order and the warp reduction is a fixed tree: the result does not depend on
+// timing.
+// Blocks are persistent and take groups of rows from a ticket counter in topological order (dependency
+// level, then row), which makes the spin-waiting deadlock free: a row only waits for rows of earlier
+// tickets, and those are resident or done.  Rows of one warp never wait for each other (one row per warp).
+// The forward sweep also arms x (the backward sweep's output) with the sentinel; the backward sweep
+// re-arms y for the next application.
+template <int P, bool FORWARD>
 __global__ void __launch_bounds__(kBlock)
-k_ilu_forward(int32_t n, const int32_t *__restrict__ order, const int32_t *__restrict__ rowptr,
-              const int32_t *__restrict__ diag, const int32_t *__restrict__ col, const double *__restrict__ lu,
-              const double *__restrict__ src, double *y, double *dst, int32_t *tickets)
+k_ilu_sweep(int32_t n, const int32_t *__restrict__ order, const int32_t *__restrict__ rowptr,
+            const int32_t *__restrict__ diag, const int32_t *__restrict__ col, const double *__restrict__ lu,
+            const double *__restrict__ src, double *y, double *x, int32_t *tickets, unsigned backoff_cap_ns)
 {
-  constexpr int ROWS = kBlock / G;
+  constexpr int ROWS = kBlock / 32;
   __shared__ int s_base;
-  if (threadIdx.x == 0)
-    {
-      const int t = atomicAdd(&tickets[0], 1);
-      if (t == 0)
-        tickets[1] = 0; // the backward sweep is not running: reset its ticket
-      s_base = t * ROWS;
-    }
-  __syncthreads();
-  const int lane = threadIdx.x % G;
-  const int p = s_base + threadIdx.x / G;
-  const unsigned gmask = group_mask<G>();
-  int r = -1, k = 0, end = 0;
-  if (p < n)
-    {
-      r = order[p];
-      k = rowptr[r] + lane;
-      end = diag[r];
-    }
-  double acc = 0.0, a = 0.0;
-  int c = 0;
-  bool loaded = false;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int my_ticket = FORWARD ? 0 : 1;
+  const double *wait_on = FORWARD ? y : x;
   for (;;)
     {
-      if (k < end)
+      __syncthreads();
+      if (threadIdx.x == 0)
         {
-          if (!loaded)
+          const int t = atomicAdd(&tickets[my_ticket], 1);
+          if (t == 0)
+            tickets[1 - my_ticket] = 0; // the other sweep is not running: reset its ticket
+          s_base = t * ROWS;
+        }
+      __syncthreads();
+      const int base = s_base;
+      if (base >= n)
+        break;
+      const int p = base + warp;
+      if (p >= n)
+        continue;
+      const int r = order[p];
+      const int beg = FORWARD ? rowptr[r] : diag[r] + 1;
+      const int end = FORWARD ? diag[r] : rowptr[r + 1];
+      // everything the last step of the row needs is fetched before the waiting starts
+      const double rhs = FORWARD ? src[r] : y[r];
+      const double inv_pivot = FORWARD ? 1.0 : lu[diag[r]];
+      double acc = 0.0;
+      for (int chunk = beg; chunk < end; chunk += 32 * P)
+        {
+          int c[P];
+          double a[P], v[P];
+          unsigned pending = 0;
+#pragma unroll
+          for (int i = 0; i < P; ++i)
             {
-              c = col[k];
-              a = lu[k];
-              loaded = true;
+              const int k = chunk + i * 32 + lane;
+              const bool valid = k < end;
+              c[i] = valid ? col[k] : 0;
+              a[i] = valid ? lu[k] : 0.0;
+              v[i] = 0.0;
+              pending |= valid ? (1u << i) : 0u;
             }
-          const double v = ld_poll(y + c);
-          if (!is_sentinel(v))
+          unsigned pause = 0;
+          for (;;)
             {
-              acc += a * v;
-              k += G;
-              loaded = false;
+#pragma unroll
+              for (int i = 0; i < P; ++i)
+                if ((pending >> i) & 1u)
+                  v[i] = ld_poll(wait_on + c[i]);
+#pragma unroll
+              for (int i = 0; i < P; ++i)
+                if (((pending >> i) & 1u) && !is_sentinel(v[i]))
+                  pending &= ~(1u << i);
+              if (!__any_sync(0xffffffffu, pending != 0u))
+                break;
+              if (pause)
+                __nanosleep(pause);
+              pause = min(pause + 16u, backoff_cap_ns);
+            }
+#pragma unroll
+          for (int i = 0; i < P; ++i)
+            acc += a[i] * v[i];
+        }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1)
+        acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (lane == 0)
+        {
+          if (FORWARD)
+            {
+              x[r] = sentinel();
+              y[r] = canonical(rhs - acc);
+            }
+          else
+            {
+              y[r] = sentinel();
+              x[r] = canonical((rhs - acc) * inv_pivot);
             }
         }
-      if (!__any_sync(gmask, k < end))
-        break;
-    }
-#pragma unroll
-  for (int o = G / 2; o > 0; o >>= 1)
-    acc += __shfl_down_sync(gmask, acc, o, G);
-  if (lane == 0 && r >= 0)
-    {
-      dst[r] = sentinel();
-      y[r] = canonical(src[r] - acc);
-    }
-}
-
-// Backward substitution: x_r = (y_r - sum_{c>r} U_rc x_c) / u_rr, inverse pivot stored on the diagonal.
-// Re-arms y for the next application.
-template <int G>
-__global__ void __launch_bounds__(kBlock)
-k_ilu_backward(int32_t n, const int32_t *__restrict__ order, const int32_t *__restrict__ rowptr,
-               const int32_t *__restrict__ diag, const int32_t *__restrict__ col, const double *__restrict__ lu, double *y,
-               double *x, int32_t *tickets)
-{
-  constexpr int ROWS = kBlock / G;
-  __shared__ int s_base;
-  if (threadIdx.x == 0)
-    {
-      const int t = atomicAdd(&tickets[1], 1);
-      if (t == 0)
-        tickets[0] = 0;
-      s_base = t * ROWS;
-    }
-  __syncthreads();
-  const int lane = threadIdx.x % G;
-  const int p = s_base + threadIdx.x / G;
-  const unsigned gmask = group_mask<G>();
-  int r = -1, k = 0, end = 0;
-  if (p < n)
-    {
-      r = order[p];
-      k = diag[r] + 1 + lane;
-      end = rowptr[r + 1];
-    }
-  double acc = 0.0, a = 0.0;
-  int c = 0;
-  bool loaded = false;
-  for (;;)
-    {
-      if (k < end)
-        {
-          if (!loaded)
-            {
-              c = col[k];
-              a = lu[k];
-              loaded = true;
-            }
-          const double v = ld_poll(x + c);
-          if (!is_sentinel(v))
-            {
-              acc += a * v;
-              k += G;
-              loaded = false;
-            }
-        }
-      if (!__any_sync(gmask, k < end))
-        break;
-    }
-#pragma unroll
-  for (int o = G / 2; o > 0; o >>= 1)
-    acc += __shfl_down_sync(gmask, acc, o, G);
-  if (lane == 0 && r >= 0)
-    {
-      const double yr = y[r];
-      y[r] = sentinel();
-      x[r] = canonical((yr - acc) * lu[diag[r]]);
     }
 }
 
@@ -242,16 +213,17 @@ k_ilu_factor(int32_t n, const int32_t *__restrict__ order, const int32_t *__rest
     }
 }
 
-template <int G>
+template <int P>
 void launch_apply(DevIlu &p, double *dst, const double *src, cudaStream_t s)
 {
   const DevMatrix &A = *p.pattern;
-  constexpr int ROWS = kBlock / G;
-  const int grid = (p.n + ROWS - 1) / ROWS;
-  S35_LAUNCH((k_ilu_forward<G>), grid, kBlock, 0, s, p.n, p.order_fwd.ptr, A.rowptr.ptr, A.diag.ptr, A.col.ptr, p.lu.ptr, src,
-             p.y.ptr, dst, p.tickets.ptr);
-  S35_LAUNCH((k_ilu_backward<G>), grid, kBlock, 0, s, p.n, p.order_bwd.ptr, A.rowptr.ptr, A.diag.ptr, A.col.ptr, p.lu.ptr,
-             p.y.ptr, dst, p.tickets.ptr);
+  constexpr int ROWS = kBlock / 32;
+  const int chunks = (p.n + ROWS - 1) / ROWS;
+  const int grid = std::min(chunks, sm_count() * p.blocks_per_sm);
+  S35_LAUNCH((k_ilu_sweep<P, true>), grid, kBlock, 0, s, p.n, p.order_fwd.ptr, A.rowptr.ptr, A.diag.ptr, A.col.ptr, p.lu.ptr,
+             src, p.y.ptr, dst, p.tickets.ptr, (unsigned)p.backoff_ns);
+  S35_LAUNCH((k_ilu_sweep<P, false>), grid, kBlock, 0, s, p.n, p.order_bwd.ptr, A.rowptr.ptr, A.diag.ptr, A.col.ptr, p.lu.ptr,
+             src, p.y.ptr, dst, p.tickets.ptr, (unsigned)p.backoff_ns);
 }
 
 } // namespace
@@ -327,16 +299,29 @@ void DevIlu::create(const DevMatrix &A, cudaStream_t s)
   ready.alloc(n);
   tickets.alloc(4);
   tickets.zero(s);
-  const double mean_lower = n ? (double)lower / n : 1.0;
-  group = 4;
-  while (group < 32 && group * 4 <= mean_lower)
-    group *= 2;
-  if (const char *g = std::getenv("S35_ILU_GROUP"))
+  // register slots per lane: one chunk of 32 * per_lane entries should hold a typical row half
+  int32_t max_half = 0;
+  for (int32_t r = 0; r < n; ++r)
+    {
+      int32_t lo = 0;
+      for (int32_t k = rp[r]; k < rp[r + 1]; ++k)
+        lo += cl[k] < r;
+      max_half = std::max(max_half, std::max(lo, rp[r + 1] - rp[r] - lo - 1));
+    }
+  per_lane = max_half <= 128 ? 2 : 4; // measured on B200: 2 beats 1 and 4 for Q1 (<= 13) and Q2 (<= ~100) rows
+  (void)lower;
+  if (const char *g = std::getenv("S35_ILU_PER_LANE"))
     {
       const int v = std::atoi(g);
-      if (v == 4 || v == 8 || v == 16 || v == 32)
-        group = v;
+      if (v == 1 || v == 2 || v == 4)
+        per_lane = v;
     }
+  blocks_per_sm = 4;
+  if (const char *g = std::getenv("S35_ILU_BLOCKS_PER_SM"))
+    blocks_per_sm = std::max(1, std::min(16, std::atoi(g)));
+  backoff_ns = 0; // measured on B200: pausing between polling rounds only adds latency
+  if (const char *g = std::getenv("S35_ILU_BACKOFF_NS"))
+    backoff_ns = std::max(0, std::min(10000, std::atoi(g)));
   factored = false;
 }
 
@@ -370,12 +355,11 @@ void DevIlu::apply(double *dst, const double *src, cudaStream_t s)
   S35_REQUIRE(dst != src, "ILU: dst must not alias src");
   if (n == 0)
     return;
-  switch (group)
+  switch (per_lane)
     {
-    case 4: launch_apply<4>(*this, dst, src, s); break;
-    case 8: launch_apply<8>(*this, dst, src, s); break;
-    case 16: launch_apply<16>(*this, dst, src, s); break;
-    default: launch_apply<32>(*this, dst, src, s); break;
+    case 1: launch_apply<1>(*this, dst, src, s); break;
+    case 2: launch_apply<2>(*this, dst, src, s); break;
+    default: launch_apply<4>(*this, dst, src, s); break;
     }
 }
 

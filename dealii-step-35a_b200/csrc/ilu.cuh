@@ -9,7 +9,7 @@
 // topological order (dependency level, then row index) through a ticket
 // counter, and a row waits for the rows it depends on.
 //  * factorisation: one warp per row, a ready flag per row;
-//  * substitution: G lanes per row; the solution vector itself is the flag --
+//  * substitution: one warp per row; the solution vector itself is the flag --
 //    it is pre-filled with a NaN bit pattern no arithmetic produces, and a
 //    consumer polls the entry it needs (through L2) until it changes.
 #pragma once
@@ -27,7 +27,9 @@ struct DevIlu
   DevBuf<int32_t> ready;              // factorisation: row finished
   DevBuf<int32_t> tickets;            // [0] forward, [1] backward, [2] factor, [3] zero-pivot flag
   int32_t levels_fwd = 0, levels_bwd = 0;
-  int group = 8;                      // lanes per row in the substitutions
+  int per_lane = 2;                   // matrix entries a lane holds in registers per chunk (one warp per row)
+  int blocks_per_sm = 4;              // resident blocks per SM of the persistent sweep kernels
+  int backoff_ns = 0;                 // longest pause between polling rounds of a waiting row
   bool factored = false;
 
   void create(const DevMatrix &A, cudaStream_t s);

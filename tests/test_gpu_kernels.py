@@ -171,7 +171,7 @@ def test_cg_matches_oracle_iteration_by_iteration(pkg, ob, make_disc, mesh, dim,
     assert ok and ok_ref
     assert st.iterations == st_ref.iterations
     # ~100 iterations of rounding differences in the recurrences: the residuals agree to a few digits
-    assert abs(st.final_residual - st_ref.final_residual) <= 1e-3 * st_ref.final_residual + 1e-300
+    assert abs(st.final_residual - st_ref.final_residual) <= 1e-2 * st_ref.final_residual + 1e-300
     assert rel_diff(x, x_ref) < 1e-8
     # iteration cap: same iterate after a fixed number of steps, and the failure is reported
     k = max(1, st_ref.iterations // 2)

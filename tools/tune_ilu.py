@@ -1,0 +1,47 @@
+"""Times the ILU(0) substitution sweeps under different launch shapes (run on the GPU box)."""
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CHILD = r'''
+import sys, os, json
+sys.path.insert(0, %r)
+import __graft_entry__ as ge
+pkg = ge.load_package()
+mesh, dim, refines = sys.argv[1], int(sys.argv[2]), int(sys.argv[3])
+params = pkg.default_params(reynolds=100.0, vel_eps=1e-8, vel_off_diagonals=0, vel_diag_strength=0.0, vel_update_prec=100,
+                            n_global_refines=refines)
+disc = pkg.Disc(os.path.join(%r, "meshes", mesh + ".s35m"), dim, params)
+ctx = pkg.Ctx(disc.problem)
+ctx.set_field(pkg.PRES_N, disc.initial_pressure)
+ctx.set_field(pkg.PRES_N_MINUS_1, disc.initial_pressure)
+ctx.advance(2, 1)
+out = {}
+for name, k in (("vel", pkg.BENCH_ILU_APPLY_VEL), ("pres", pkg.BENCH_ILU_APPLY_PRES), ("factor", pkg.BENCH_ILU_FACTOR_VEL)):
+    ms, nbytes, _ = ctx.bench_kernel(k, warmup=2, reps=5, flush_l2=False)
+    out[name] = ms
+print(json.dumps(out))
+''' % (ROOT, ROOT)
+
+
+def main():
+    mesh, dim, refines = sys.argv[1], sys.argv[2], sys.argv[3]
+    variants = [{}]
+    for p in (1, 2, 4):
+        variants.append({"S35_ILU_PER_LANE": str(p)})
+    for b in (1, 2, 8):
+        variants.append({"S35_ILU_BLOCKS_PER_SM": str(b)})
+    for ns in (0, 32, 256, 1000):
+        variants.append({"S35_ILU_BACKOFF_NS": str(ns)})
+    variants.append({"S35_ILU_BACKOFF_NS": "0", "S35_ILU_BLOCKS_PER_SM": "1"})
+    for v in variants:
+        env = dict(os.environ)
+        env.update(v)
+        r = subprocess.run([sys.executable, "-c", CHILD, mesh, dim, refines], env=env, capture_output=True, text=True)
+        print(json.dumps(v), r.stdout.strip() or r.stderr[-500:], flush=True)
+
+
+if __name__ == "__main__":
+    main()
