@@ -174,7 +174,8 @@ def test_cg_matches_oracle_iteration_by_iteration(pkg, ob, make_disc, mesh, dim,
     assert abs(st.final_residual - st_ref.final_residual) <= 1e-2 * st_ref.final_residual + 1e-300
     assert rel_diff(x, x_ref) < 1e-8
     # iteration cap: same iterate after a fixed number of steps, and the failure is reported
-    k = max(1, st_ref.iterations // 2)
+    # (a handful of steps: later CG iterates are sensitive to rounding long before the solution is)
+    k = min(5, max(1, st_ref.iterations // 2))
     xk_ref, stk_ref, okk_ref = ob.cg(n, rp, cl, val, lu, np.zeros(n), b, 0.0, max_its=k)
     xk, stk, okk = pkg.cg(A, P, np.zeros(n), b, 0.0, max_iterations=k)
     assert not okk and not okk_ref and stk.iterations == k == stk_ref.iterations

@@ -179,3 +179,23 @@ def test_simulation_driver_runs_like_the_reference_loop(pkg, ob, make_disc, tmp_
     assert os.path.exists(tmp_path / "solution-000000001.h5")
     ms, calls = sim.ctx.section_ms("projection_step_solve")
     assert calls == 9 and ms > 0
+
+
+GOLDEN_TOL = {"nsbench2_r0_steps8.npz": 1e-8, "nsbench2_r1_steps5.npz": 5e-8, "cylinder3d_r0_steps2.npz": 1e-8}
+
+
+@pytest.mark.parametrize("name", sorted(GOLDEN_TOL))
+def test_device_path_reproduces_the_golden_vectors(pkg, make_disc, name):
+    """fixtures from the independent numpy restatement (tools/make_golden.py), compared by support point"""
+    import os
+    from conftest import GOLDEN_DIR
+    from test_oracle import check_against_golden
+    g = np.load(os.path.join(GOLDEN_DIR, name))
+    dim, refines, steps = int(g["dim"]), int(g["refines"]), int(g["steps"])
+    disc = make_disc(str(g["mesh"]) + ".s35m", dim, n_global_refines=refines, reynolds=float(g["reynolds"]))
+    ctx = pkg.Ctx(disc.problem)
+    start_state(pkg, disc, ctx)
+    ctx.advance(2, steps)
+    assert [ctx.solver_stats(d).iterations for d in range(dim)] == list(g["its_vel"])
+    assert abs(ctx.solver_stats(-1).iterations - int(g["its_proj"])) <= 1
+    check_against_golden(pkg, disc, ctx, g, GOLDEN_TOL[name])
