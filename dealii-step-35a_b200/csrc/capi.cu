@@ -464,7 +464,7 @@ s35_status s35_ctx_bench_kernel(s35_ctx *ctx, s35_bench_kernel kernel, int32_t w
     cudaStream_t s = c.stream;
     double bytes = 0.0;
     // scratch operands: GMRES work vectors (velocity sized) and CG work vectors (pressure sized)
-    double *xv = c.gmres.tmp.ptr, *yv = c.gmres.tmp.ptr + c.gmres.stride, *zv = c.gmres.tmp.ptr + 2 * c.gmres.stride;
+    double *xv = c.gmres[0].tmp.ptr, *yv = c.gmres[0].tmp.ptr + c.gmres[0].stride, *zv = c.gmres[0].tmp.ptr + 2 * c.gmres[0].stride;
     double *xp = c.cg.g, *yp = c.cg.d;
     vec_set(xv, 1.0, c.nv, s);
     vec_set(yv, 0.5, c.nv, s);

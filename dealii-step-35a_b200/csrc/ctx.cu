@@ -3,6 +3,8 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <exception>
+#include <thread>
 
 namespace s35 {
 
@@ -146,7 +148,18 @@ Ctx::Ctx(const s35_problem &p)
   prec_pres.create(plap, s);
   prec_pres.factor(plap.val, diag_strength, s);
   prec_pres.check_pivots(s);
-  gmres.init(nv, krylov, s);
+  concurrent_components = true;
+  if (const char *t = std::getenv("S35_CONCURRENT_COMPONENTS"))
+    concurrent_components = std::atoi(t) != 0;
+  S35_CUDA(cudaEventCreateWithFlags(&fork_event, cudaEventDisableTiming));
+  for (int d = 0; d < dim; ++d)
+    {
+      S35_CUDA(cudaStreamCreateWithFlags(&comp_stream[d], cudaStreamNonBlocking));
+      S35_CUDA(cudaEventCreateWithFlags(&join_event[d], cudaEventDisableTiming));
+      gmres[d].init(nv, krylov, concurrent_components ? comp_stream[d] : s);
+      ws_comp[d].init(concurrent_components ? comp_stream[d] : s);
+      S35_CUDA(cudaStreamSynchronize(comp_stream[d]));
+    }
   cg.init(np, s);
   ws.init(s);
   scal.alloc(8);
@@ -178,6 +191,15 @@ Ctx::~Ctx()
     }
   for (auto e : event_pool)
     cudaEventDestroy(e);
+  if (fork_event)
+    cudaEventDestroy(fork_event);
+  for (int d = 0; d < 3; ++d)
+    {
+      if (join_event[d])
+        cudaEventDestroy(join_event[d]);
+      if (comp_stream[d])
+        cudaStreamDestroy(comp_stream[d]);
+    }
   if (stream)
     cudaStreamDestroy(stream);
 }
@@ -268,7 +290,32 @@ void Ctx::assemble_advection_term()
   end_section(sec);
 }
 
-// step-35a.cc:1268-1338
+// One velocity component of the second half of diffusion_step (step-35a.cc:1308-1324), on stream `s`.
+void Ctx::solve_component(int d, bool reinit_prec, cudaStream_t s)
+{
+  flow[d].condense(vel_adv, it_val[d], force[d], scal.ptr + 0, s);
+  if (reinit_prec)
+    {
+      prec_vel[d].factor(it_val[d], diag_strength, s);
+      prec_vel[d].check_pivots(s);
+    }
+  vec_dot(scal.ptr + 1 + d, force[d], force[d], nv, kSqrt, ws_comp[d], s);
+  S35_CUDA(cudaMemcpyAsync(scal_host.ptr + 1 + d, scal.ptr + 1 + d, sizeof(double), cudaMemcpyDeviceToHost, s));
+  S35_CUDA(cudaStreamSynchronize(s));
+  const double tol = eps * scal_host.ptr[1 + d];
+  const bool ok = gmres[d].solve(vel_adv, it_val[d], prec_vel[d], u_n[d], force[d], tol, max_its, stats_vel[d]);
+  if (!ok)
+    throw Error(S35_ERR_NO_CONVERGENCE, "GMRES did not converge for velocity component " + std::to_string(d) + " after " +
+                                          std::to_string(stats_vel[d].iterations) + " iterations, residual " +
+                                          std::to_string(stats_vel[d].final_residual));
+  vec_scatter_set(u_n[d], flow[d].dofs, flow[d].values, flow[d].n_constrained, s); // flow constraints distribute
+  vec_scatter_set(u_n[d], wall_dofs, nullptr, n_wall, s);                          // wall constraints distribute
+}
+
+// step-35a.cc:1268-1338.  The reference runs the dim components as concurrent tasks (Threads::new_task,
+// step-35a.cc:1277-1325); here every component has its own stream, and the host-driven GMRES loops run in
+// one host thread per component.  The substitution sweeps are latency bound, so the dim solves overlap almost
+// perfectly on the device.
 void Ctx::diffusion_step(bool reinit_prec)
 {
   cudaStream_t s = stream;
@@ -276,42 +323,77 @@ void Ctx::diffusion_step(bool reinit_prec)
   vec_lincomb3(pres_tmp, DScal(-1.0), pres_n, DScal(-4.0 / 3.0), phi_n, DScal(1.0 / 3.0), phi_nm1, np, s);
   {
     const size_t sec = begin_section("setup_diffusion_rhs");
+    S35_CUDA(cudaEventRecord(fork_event, s));
     for (int d = 0; d < dim; ++d)
       {
-        vec_lincomb(v_tmp[d], DScal(2.0 / dt), u_n[d], DScal(-0.5 / dt), u_nm1[d], nv, s);
-        spmv(vel_mass, v_tmp[d], force[d], false, s);                       // force = 0 + vel_Mass v_tmp
-        spmv_values(grad, grad_val[d], pres_tmp, force[d], true, s);        // force += pres_Diff[d] pres_tmp
-        vec_copy(u_nm1[d], u_n[d], nv, s);
-        vec_copy(it_val[d], vel_adv.val, vel_adv.nnz, s);                   // vel_it_matrix[d].copy_from(vel_Advection)
+        cudaStream_t sd = concurrent_components ? comp_stream[d] : s;
+        if (concurrent_components)
+          S35_CUDA(cudaStreamWaitEvent(sd, fork_event, 0));
+        vec_lincomb(v_tmp[d], DScal(2.0 / dt), u_n[d], DScal(-0.5 / dt), u_nm1[d], nv, sd);
+        spmv(vel_mass, v_tmp[d], force[d], false, sd);                       // force = 0 + vel_Mass v_tmp
+        spmv_values(grad, grad_val[d], pres_tmp, force[d], true, sd);        // force += pres_Diff[d] pres_tmp
+        vec_copy(u_nm1[d], u_n[d], nv, sd);
+        vec_copy(it_val[d], vel_adv.val, vel_adv.nnz, sd);                   // vel_it_matrix[d].copy_from(vel_Advection)
+        if (concurrent_components)
+          {
+            S35_CUDA(cudaEventRecord(join_event[d], sd));
+            S35_CUDA(cudaStreamWaitEvent(s, join_event[d], 0));
+          }
       }
     end_section(sec);
   }
   {
     const size_t sec = begin_section("solve_diffusion_component");
     diag_abs_mean(vel_adv, vel_adv.val, scal.ptr + 0, ws, s);
-    for (int d = 0; d < dim; ++d)
+    if (!concurrent_components)
       {
-        flow[d].condense(vel_adv, it_val[d], force[d], scal.ptr + 0, s);
-        if (reinit_prec)
+        try
           {
-            prec_vel[d].factor(it_val[d], diag_strength, s);
-            prec_vel[d].check_pivots(s);
+            for (int d = 0; d < dim; ++d)
+              solve_component(d, reinit_prec, s);
           }
-        vec_dot(scal.ptr + 1 + d, force[d], force[d], nv, kSqrt, ws, s);
-        S35_CUDA(cudaMemcpyAsync(scal_host.ptr + 1 + d, scal.ptr + 1 + d, sizeof(double), cudaMemcpyDeviceToHost, s));
-        S35_CUDA(cudaStreamSynchronize(s));
-        const double tol = eps * scal_host.ptr[1 + d];
-        const bool ok = gmres.solve(vel_adv, it_val[d], prec_vel[d], u_n[d], force[d], tol, max_its, stats_vel[d]);
-        if (!ok)
+        catch (...)
           {
             end_section(sec);
             resolve_sections();
-            throw Error(S35_ERR_NO_CONVERGENCE, "GMRES did not converge for velocity component " + std::to_string(d) +
-                                                  " after " + std::to_string(stats_vel[d].iterations) + " iterations, residual " +
-                                                  std::to_string(stats_vel[d].final_residual));
+            throw;
           }
-        vec_scatter_set(u_n[d], flow[d].dofs, flow[d].values, flow[d].n_constrained, s); // flow constraints distribute
-        vec_scatter_set(u_n[d], wall_dofs, nullptr, n_wall, s);                          // wall constraints distribute
+      }
+    else
+      {
+        S35_CUDA(cudaEventRecord(fork_event, s));
+        std::exception_ptr failure[3];
+        std::thread workers[3];
+        for (int d = 0; d < dim; ++d)
+          {
+            S35_CUDA(cudaStreamWaitEvent(comp_stream[d], fork_event, 0));
+            workers[d] = std::thread([this, d, reinit_prec, &failure] {
+              try
+                {
+                  S35_CUDA(cudaSetDevice(device));
+                  solve_component(d, reinit_prec, comp_stream[d]);
+                  S35_CUDA(cudaEventRecord(join_event[d], comp_stream[d]));
+                }
+              catch (...)
+                {
+                  failure[d] = std::current_exception();
+                }
+            });
+          }
+        for (int d = 0; d < dim; ++d)
+          workers[d].join();
+        for (int d = 0; d < dim; ++d)
+          if (!failure[d])
+            S35_CUDA(cudaStreamWaitEvent(s, join_event[d], 0));
+        for (int d = 0; d < dim; ++d)
+          if (failure[d])
+            {
+              for (int e = 0; e < dim; ++e)
+                cudaStreamSynchronize(comp_stream[e]);
+              end_section(sec);
+              resolve_sections();
+              std::rethrow_exception(failure[d]);
+            }
       }
     end_section(sec);
   }

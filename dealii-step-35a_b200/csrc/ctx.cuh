@@ -45,7 +45,11 @@ struct Ctx
 
   // preconditioners and solvers
   DevIlu prec_vel[3], prec_pres;
-  GmresSolver gmres;
+  GmresSolver gmres[3];           // one per velocity component
+  ReduceWs ws_comp[3];
+  cudaStream_t comp_stream[3] = {nullptr, nullptr, nullptr};
+  cudaEvent_t fork_event = nullptr, join_event[3] = {nullptr, nullptr, nullptr};
+  bool concurrent_components = true;
   CgSolver cg;
   AdvectionAssembler assembler;
   ReduceWs ws;
@@ -77,6 +81,7 @@ struct Ctx
   void interpolate_velocity();
   void assemble_advection_term();
   void diffusion_step(bool reinit_prec);
+  void solve_component(int d, bool reinit_prec, cudaStream_t s);
   void projection_step();
   void update_pressure();
   void advance(int first_n, int n_steps, int start_n, int start_offset_n, double *elapsed_ms);

@@ -1,4 +1,7 @@
-"""Times the ILU(0) substitution sweeps under different launch shapes (run on the GPU box)."""
+"""Times the ILU(0) substitution sweeps under different launch shapes (run on the GPU box).
+
+    python tools/tune_ilu.py <mesh> <dim> <refines> [variant-set]
+"""
 import json
 import os
 import subprocess
@@ -17,30 +20,31 @@ disc = pkg.Disc(os.path.join(%r, "meshes", mesh + ".s35m"), dim, params)
 ctx = pkg.Ctx(disc.problem)
 ctx.set_field(pkg.PRES_N, disc.initial_pressure)
 ctx.set_field(pkg.PRES_N_MINUS_1, disc.initial_pressure)
-ctx.advance(2, 1)
-out = {}
-for name, k in (("vel", pkg.BENCH_ILU_APPLY_VEL), ("pres", pkg.BENCH_ILU_APPLY_PRES), ("factor", pkg.BENCH_ILU_FACTOR_VEL)):
+ms_step = ctx.advance(2, 2) / 2
+out = {"step_ms": round(ms_step, 2), "its": [ctx.solver_stats(d).iterations for d in range(dim)] + [ctx.solver_stats(-1).iterations]}
+for name, k in (("vel", pkg.BENCH_ILU_APPLY_VEL), ("pres", pkg.BENCH_ILU_APPLY_PRES)):
     ms, nbytes, _ = ctx.bench_kernel(k, warmup=2, reps=5, flush_l2=False)
-    out[name] = ms
+    out[name] = round(ms, 3)
 print(json.dumps(out))
 ''' % (ROOT, ROOT)
+
+VARIANT_SETS = {
+    "default": [{}],
+    "multi": [{}] + [{"S35_ILU_PER_LANE": str(p)} for p in (1, 2, 4)] + [{"S35_ILU_BLOCKS_PER_SM": str(b)} for b in (1, 2, 8)],
+    "cta": [{}] + [{"S35_ILU_MODE": "cta", "S35_ILU_CTA_G": str(g), "S35_ILU_CTA_P": str(p)}
+                   for g, p in ((8, 2), (8, 4), (16, 2), (16, 4), (32, 2))],
+}
 
 
 def main():
     mesh, dim, refines = sys.argv[1], sys.argv[2], sys.argv[3]
-    variants = [{}]
-    for p in (1, 2, 4):
-        variants.append({"S35_ILU_PER_LANE": str(p)})
-    for b in (1, 2, 8):
-        variants.append({"S35_ILU_BLOCKS_PER_SM": str(b)})
-    for ns in (0, 32, 256, 1000):
-        variants.append({"S35_ILU_BACKOFF_NS": str(ns)})
-    variants.append({"S35_ILU_BACKOFF_NS": "0", "S35_ILU_BLOCKS_PER_SM": "1"})
+    variants = VARIANT_SETS[sys.argv[4] if len(sys.argv) > 4 else "default"]
     for v in variants:
         env = dict(os.environ)
         env.update(v)
-        r = subprocess.run([sys.executable, "-c", CHILD, mesh, dim, refines], env=env, capture_output=True, text=True)
-        print(json.dumps(v), r.stdout.strip() or r.stderr[-500:], flush=True)
+        r = subprocess.run([sys.executable, "-c", CHILD, mesh, dim, refines], env=env, capture_output=True, text=True,
+                           timeout=600)
+        print(json.dumps(v), r.stdout.strip() or r.stderr[-800:], flush=True)
 
 
 if __name__ == "__main__":
