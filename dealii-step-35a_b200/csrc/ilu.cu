@@ -132,89 +132,6 @@ k_ilu_sweep(int32_t n, const int32_t *__restrict__ order, const int32_t *__restr
     }
 }
 
-__device__ __forceinline__ double ld_cta(const double *p)
-{
-  double v;
-  asm volatile("ld.relaxed.cta.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_cta(double *p, double v)
-{
-  asm volatile("st.relaxed.cta.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
-}
-
-// EXPERIMENT (S35_ILU_MODE=cta): the whole sweep in ONE thread block.  Producer and consumer rows then sit on
-// the same SM and exchange solution entries with CTA-scope loads and stores, i.e. through L1 (~30 cycles)
-// instead of L2 (~300 cycles).  G lanes per row, rows dealt round-robin to the 1024 / G groups in level order.
-template <int G, int P, bool FORWARD>
-__global__ void __launch_bounds__(1024, 1)
-k_ilu_sweep_cta(int32_t n, const int32_t *__restrict__ order, const int32_t *__restrict__ rowptr,
-                const int32_t *__restrict__ diag, const int32_t *__restrict__ col, const double *__restrict__ lu,
-                const double *__restrict__ src, double *y, double *x)
-{
-  constexpr int ROWS = 1024 / G;
-  const int lane = threadIdx.x % G, grp = threadIdx.x / G;
-  const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << (G & 31)) - 1u) << (((threadIdx.x & 31) / G) * G));
-  const double *wait_on = FORWARD ? y : x;
-  for (int p = grp; p < n; p += ROWS)
-    {
-      const int r = order[p];
-      const int beg = FORWARD ? rowptr[r] : diag[r] + 1;
-      const int end = FORWARD ? diag[r] : rowptr[r + 1];
-      const double rhs = FORWARD ? src[r] : ld_cta(y + r);
-      const double inv_pivot = FORWARD ? 1.0 : lu[diag[r]];
-      double acc = 0.0;
-      for (int chunk = beg; __any_sync(gmask, chunk < end); chunk += G * P)
-        {
-          int c[P];
-          double a[P], v[P];
-          unsigned pending = 0;
-#pragma unroll
-          for (int i = 0; i < P; ++i)
-            {
-              const int k = chunk + i * G + lane;
-              const bool valid = k < end;
-              c[i] = valid ? col[k] : 0;
-              a[i] = valid ? lu[k] : 0.0;
-              v[i] = 0.0;
-              pending |= valid ? (1u << i) : 0u;
-            }
-          for (;;)
-            {
-#pragma unroll
-              for (int i = 0; i < P; ++i)
-                if ((pending >> i) & 1u)
-                  v[i] = ld_cta(wait_on + c[i]);
-#pragma unroll
-              for (int i = 0; i < P; ++i)
-                if (((pending >> i) & 1u) && !is_sentinel(v[i]))
-                  pending &= ~(1u << i);
-              if (!__any_sync(gmask, pending != 0u))
-                break;
-            }
-#pragma unroll
-          for (int i = 0; i < P; ++i)
-            acc += a[i] * v[i];
-        }
-#pragma unroll
-      for (int o = G / 2; o > 0; o >>= 1)
-        acc += __shfl_xor_sync(gmask, acc, o, G);
-      if (lane == 0)
-        {
-          if (FORWARD)
-            {
-              st_cta(x + r, sentinel());
-              st_cta(y + r, canonical(rhs - acc));
-            }
-          else
-            {
-              st_cta(y + r, sentinel());
-              st_cta(x + r, canonical((rhs - acc) * inv_pivot));
-            }
-        }
-    }
-}
-
 // lu = a, optionally with deal.II's diagonal strengthening:
 // a_rr += strengthen * sum_{c != r} |a_rc|  (SparseLUDecomposition::strengthen_diagonal_impl)
 __global__ void k_ilu_prepare(int32_t n, const int32_t *__restrict__ rowptr, const int32_t *__restrict__ diag,
@@ -438,29 +355,6 @@ void DevIlu::apply(double *dst, const double *src, cudaStream_t s)
   S35_REQUIRE(dst != src, "ILU: dst must not alias src");
   if (n == 0)
     return;
-  static const char *mode = std::getenv("S35_ILU_MODE");
-  if (mode && std::strcmp(mode, "cta") == 0)
-    {
-      static const int g = std::getenv("S35_ILU_CTA_G") ? std::atoi(std::getenv("S35_ILU_CTA_G")) : 8;
-      static const int pl = std::getenv("S35_ILU_CTA_P") ? std::atoi(std::getenv("S35_ILU_CTA_P")) : 2;
-      const DevMatrix &A = *pattern;
-#define S35_CTA_CASE(G, P)                                                                                                \
-  if (g == G && pl == P)                                                                                                  \
-    {                                                                                                                     \
-      S35_LAUNCH((k_ilu_sweep_cta<G, P, true>), 1, 1024, 0, s, n, order_fwd.ptr, A.rowptr.ptr, A.diag.ptr, A.col.ptr,     \
-                 lu.ptr, src, y.ptr, dst);                                                                                \
-      S35_LAUNCH((k_ilu_sweep_cta<G, P, false>), 1, 1024, 0, s, n, order_bwd.ptr, A.rowptr.ptr, A.diag.ptr, A.col.ptr,    \
-                 lu.ptr, src, y.ptr, dst);                                                                                \
-      return;                                                                                                             \
-    }
-      S35_CTA_CASE(8, 2)
-      S35_CTA_CASE(8, 4)
-      S35_CTA_CASE(16, 2)
-      S35_CTA_CASE(16, 4)
-      S35_CTA_CASE(32, 2)
-#undef S35_CTA_CASE
-      throw Error(S35_ERR_INVALID, "S35_ILU_MODE=cta: unsupported G / P");
-    }
   switch (per_lane)
     {
     case 1: launch_apply<1>(*this, dst, src, s); break;
