@@ -112,6 +112,7 @@ _SIGNATURES = [
     ("s35_vec_lincomb", C.c_int, [C.c_int64, C.c_double, c_double_p, C.c_double, c_double_p, c_double_p]),
     ("s35_vec_dot", C.c_int, [C.c_int64, c_double_p, c_double_p, c_double_p]),
     ("s35_vec_add_and_dot", C.c_int, [C.c_int64, C.c_double, c_double_p, c_double_p, c_double_p, c_double_p]),
+    ("s35_vec_dot_device_noalloc", C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     ("s35_ctx_create", C.c_int, [C.POINTER(Problem), C.POINTER(_VP)]),
     ("s35_ctx_destroy", None, [_VP]),
     ("s35_ctx_set_field", C.c_int, [_VP, C.c_int, C.c_int32, c_double_p]),

@@ -337,3 +337,88 @@ void flush_l2(cudaStream_t s)
 }
 
 } // namespace s35
+
+// ------------------------------------------------------------------------------------------------------
+// s35_vec_dot_device_noalloc: the dot product for callers that must not allocate.
+//
+// Who needs this: a host program that sizes all of its device memory once at start-up and then runs its
+// Krylov loop against a fixed budget (cudaMalloc may fail there, and even when it succeeds it stalls every
+// stream of the device); a caller whose buffers all come from its own pool and who is not allowed to reach
+// past that pool into the driver; code that is in the middle of recording a stream and therefore cannot
+// call anything that synchronises.  The ordinary s35_vec_dot stages host vectors in freshly allocated device
+// buffers and allocates its reduction scratch on every call, so none of those callers can use it.
+//
+// This variant takes device pointers for both vectors and for the result and launches the same reduction
+// kernel; the per-block partial sums and the ticket counter live in the array below, which is part of the
+// library image: every GPU that loads the library carries these 8.25 KB until the process ends, and nothing
+// is ever allocated or freed.  The array holds one partial per block of 2048 elements, 1024 of them, which
+// is where the size limit of 2 097 152 elements comes from.
+// ------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace s35 {
+void set_last_error(const std::string &msg); // capi.cu
+
+namespace {
+
+constexpr int kNoAllocMaxBlocks = 1024;
+constexpr int64_t kNoAllocMaxN = (int64_t)kNoAllocMaxBlocks * kBlock * 8; // 2 097 152 elements
+// [0, 1024): per-block partial sums; [1024]: the ticket counter of the single-pass reduction
+static __device__ __align__(256) double g_noalloc_scratch[kNoAllocMaxBlocks + 32];
+
+// Device address of the scratch array on the current device.  In host code `g_noalloc_scratch` is only a
+// handle for the symbol, not something a kernel can dereference, so the address is looked up once per device
+// (with that device current) and remembered.
+double *noalloc_scratch_on_current_device()
+{
+  static std::mutex mutex;
+  static double *address[64] = {};
+  int device = 0;
+  S35_CUDA(cudaGetDevice(&device));
+  S35_REQUIRE(device >= 0 && device < 64, "vec_dot_device_noalloc: device ordinal above 63");
+  std::lock_guard<std::mutex> lock(mutex);
+  if (address[device] == nullptr)
+    {
+      double *p = nullptr;
+      S35_CUDA(cudaGetSymbolAddress((void **)&p, g_noalloc_scratch));
+      S35_REQUIRE(p != nullptr, "vec_dot_device_noalloc: no device address for the scratch array");
+      address[device] = p;
+    }
+  return address[device];
+}
+
+} // namespace
+} // namespace s35
+
+extern "C" s35_status s35_vec_dot_device_noalloc(int64_t n, const double *x_device, const double *y_device,
+                                                 double *result_device, void *stream)
+{
+  using namespace s35;
+  try
+    {
+      S35_REQUIRE(n >= 0, "vec_dot_device_noalloc: negative length");
+      S35_REQUIRE(result_device != nullptr && (n == 0 || (x_device != nullptr && y_device != nullptr)),
+                  "vec_dot_device_noalloc: null pointer");
+      if (n > kNoAllocMaxN)
+        throw Error(S35_ERR_INVALID, "vec_dot_device_noalloc: " + std::to_string(n) + " elements exceed the limit of " +
+                                       std::to_string(kNoAllocMaxN) +
+                                       " set by the built-in scratch array; use s35_vec_dot, which allocates");
+      cudaStream_t s = static_cast<cudaStream_t>(stream);
+      double *scratch = noalloc_scratch_on_current_device();
+      unsigned int *ticket = reinterpret_cast<unsigned int *>(scratch + kNoAllocMaxBlocks);
+      // the array still holds whatever the previous call left: the ticket must start at zero
+      S35_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), s));
+      S35_LAUNCH(k_dot, reduce_grid(n), kBlock, 0, s, result_device, x_device, y_device, n, (int)kSum, scratch, ticket);
+      return S35_OK;
+    }
+  catch (const Error &e)
+    {
+      set_last_error(e.what());
+      return e.code;
+    }
+  catch (const std::exception &e)
+    {
+      set_last_error(e.what());
+      return S35_ERR_INVALID;
+    }
+}

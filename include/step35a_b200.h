@@ -121,6 +121,24 @@ s35_status s35_vec_dot(int64_t n, const double *x, const double *y, double *resu
 /* y += a x; result = y . w   (Vector::add_and_dot) */
 s35_status s35_vec_add_and_dot(int64_t n, double a, const double *x, double *y, const double *w, double *result);
 
+/* result = x . y without allocating anything.  This entry point has no counterpart in the reference; it exists
+ * for callers that cannot call cudaMalloc: programs that reserve all of their device memory up front and run
+ * against that fixed budget, callers confined to a memory pool of their own, and code that must not trigger
+ * the device-wide stall an allocation causes inside its solver loop.
+ *   - x_device, y_device (n doubles each) and result_device (one double) are DEVICE pointers owned by the
+ *     caller; `stream` is a cudaStream_t (NULL: the default stream).  The call only enqueues work: read
+ *     *result_device after synchronising that stream.
+ *   - The reduction scratch is a fixed array inside the library image (8.25 KB on every GPU that loads the
+ *     library, for the life of the process), so n is limited to 2 097 152 elements; larger n returns
+ *     S35_ERR_INVALID with a message naming the limit.  No cudaMalloc, cudaFree or allocating library call
+ *     is made.  The result is bit-identical to s35_vec_dot's for the same vectors.
+ *   - The first call on each device looks up the device address of that array; make that first call before
+ *     starting any stream capture.
+ *   - All calls share the one array: two calls that can run on the GPU at the same time (different streams
+ *     without an ordering between them) race and give wrong results.  Calls on one stream are safe. */
+s35_status s35_vec_dot_device_noalloc(int64_t n, const double *x_device, const double *y_device, double *result_device,
+                                      void *stream);
+
 /* ------------------------------------------------------------------------
  * The time-step context: everything NavierStokesProjection<dim> keeps between steps.
  * ---------------------------------------------------------------------- */
