@@ -43,6 +43,18 @@ class SolverStats(C.Structure):
                 ("tolerance", C.c_double)]
 
 
+class Halo(C.Structure):
+    _fields_ = [("n_neighbors", C.c_int32), ("neighbor_rank", c_int32_p), ("send_ptr", c_int32_p), ("send_idx", c_int32_p),
+                ("recv_ptr", c_int32_p)]
+
+
+class Dist(C.Structure):
+    _fields_ = [("rank", C.c_int32), ("n_ranks", C.c_int32), ("n_vel_owned", C.c_int32), ("n_pres_owned", C.c_int32),
+                ("n_vel_global", C.c_int64), ("n_pres_global", C.c_int64), ("vel_halo", Halo), ("pres_halo", Halo),
+                ("vel_global_index", c_int32_p), ("pres_global_index", c_int32_p),
+                ("gradT_rowptr", c_int32_p), ("gradT_col", c_int32_p), ("gradT_val", c_double_p * 3)]
+
+
 class Problem(C.Structure):
     _fields_ = [
         ("dim", C.c_int32), ("n_cells", C.c_int32), ("n_vel", C.c_int32), ("n_pres", C.c_int32),
@@ -58,6 +70,7 @@ class Problem(C.Structure):
         ("dt", C.c_double), ("reynolds", C.c_double), ("vel_eps", C.c_double), ("vel_diag_strength", C.c_double),
         ("vel_max_iterations", C.c_int32), ("vel_krylov_size", C.c_int32), ("vel_off_diagonals", C.c_int32),
         ("vel_update_prec", C.c_int32), ("rotational", C.c_int32),
+        ("dist", C.POINTER(Dist)),
     ]
 
 
@@ -113,6 +126,11 @@ _SIGNATURES = [
     ("s35_vec_dot", C.c_int, [C.c_int64, c_double_p, c_double_p, c_double_p]),
     ("s35_vec_add_and_dot", C.c_int, [C.c_int64, C.c_double, c_double_p, c_double_p, c_double_p, c_double_p]),
     ("s35_vec_dot_device_noalloc", C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    ("s35_comm_unique_id", C.c_int, [C.c_char_p]),
+    ("s35_comm_init", C.c_int, [C.c_int32, C.c_int32, C.c_char_p]),
+    ("s35_comm_finalize", None, []),
+    ("s35_comm_thread_group", C.c_int, [C.c_int32]),
+    ("s35_comm_thread_bind", C.c_int, [C.c_int32]),
     ("s35_ctx_create", C.c_int, [C.POINTER(Problem), C.POINTER(_VP)]),
     ("s35_ctx_destroy", None, [_VP]),
     ("s35_ctx_set_field", C.c_int, [_VP, C.c_int, C.c_int32, c_double_p]),
@@ -143,6 +161,11 @@ _SIGNATURES = [
     ("s35_disc_mesh", C.c_int, [_VP, C.POINTER(c_double_p), C.POINTER(c_int32_p), C.POINTER(c_int32_p),
                                 C.POINTER(c_int32_p), C.POINTER(C.c_int64)]),
     ("s35_disc_pres_cell_dofs", c_int32_p, [_VP]),
+    ("s35_part_create", C.c_int, [_VP, C.c_int32, C.c_int32, C.POINTER(_VP)]),
+    ("s35_part_destroy", None, [_VP]),
+    ("s35_part_problem", C.POINTER(Problem), [_VP]),
+    ("s35_part_initial_pressure", c_double_p, [_VP]),
+    ("s35_disc_partition_cells", C.c_int, [_VP, C.c_int32, c_int32_p]),
     ("s35_mesh_convert", C.c_int, [C.c_char_p, C.c_int32, C.c_char_p]),
     ("s35_sim_create", C.c_int, [C.POINTER(Params), C.c_char_p, C.c_int32, C.POINTER(_VP)]),
     ("s35_sim_destroy", None, [_VP]),
@@ -309,6 +332,88 @@ class Disc:
         p = f64(p)
         check(lib().s35_disc_drag_lift(self.handle, reynolds, dptr(u), dptr(p), dptr(out)))
         return out
+
+
+class Part:
+    """One rank's part of a mesh-partitioned problem (s35_part): local problem, ownership and halo plans."""
+
+    def __init__(self, disc, n_ranks, rank):
+        h = _VP()
+        check(lib().s35_part_create(disc.handle, n_ranks, rank, C.byref(h)))
+        self.handle = h
+        self.disc = disc
+        self.problem = lib().s35_part_problem(h)
+        p = self.problem.contents
+        d = p.dist.contents
+        self.rank, self.n_ranks, self.dim = d.rank, d.n_ranks, p.dim
+        self.nv, self.np_ = p.n_vel, p.n_pres
+        self.nv_owned, self.np_owned = d.n_vel_owned, d.n_pres_owned
+        self.vel_global = _view(d.vel_global_index, (self.nv,), np.int32)
+        self.pres_global = _view(d.pres_global_index, (self.np_,), np.int32)
+        self.initial_pressure = _view(lib().s35_part_initial_pressure(h), (self.np_,), np.float64)
+
+    def halo(self, which):
+        d = self.problem.contents.dist.contents
+        hl = d.vel_halo if which == "vel" else d.pres_halo
+        nb = _view(hl.neighbor_rank, (hl.n_neighbors,), np.int32)
+        sp_ = _view(hl.send_ptr, (hl.n_neighbors + 1,), np.int32)
+        rp = _view(hl.recv_ptr, (hl.n_neighbors + 1,), np.int32)
+        si = _view(hl.send_idx, (int(sp_[-1]) if hl.n_neighbors else 0,), np.int32)
+        return nb, sp_, si, rp
+
+    def csr(self, which):
+        """local rows (owned DoFs) of 'velc', 'velm', 'grad', 'gradT', 'plap', 'pmass': (rowptr, col, values)"""
+        p = self.problem.contents
+        d = p.dist.contents
+        if which == "gradT":
+            rowptr = _view(d.gradT_rowptr, (self.np_owned + 1,), np.int32)
+            nnz = int(rowptr[-1])
+            return rowptr, _view(d.gradT_col, (nnz,), np.int32), [_view(d.gradT_val[k], (nnz,), np.float64) for k in range(self.dim)]
+        n_rows = self.nv_owned if which in ("velc", "velm", "grad") else self.np_owned
+        rowptr = _view(getattr(p, which + "_rowptr"), (n_rows + 1,), np.int32)
+        nnz = int(rowptr[-1])
+        col = _view(getattr(p, which + "_col"), (nnz,), np.int32)
+        if which == "velc":
+            val = None
+        elif which == "grad":
+            val = [_view(p.grad_val[k], (nnz,), np.float64) for k in range(self.dim)]
+        else:
+            val = _view(getattr(p, which + "_val"), (nnz,), np.float64)
+        return rowptr, col, val
+
+    def close(self):
+        if self.handle is not None:
+            lib().s35_part_destroy(self.handle)
+        self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def comm_unique_id():
+    buf = C.create_string_buffer(128)
+    check(lib().s35_comm_unique_id(buf))
+    return buf.raw
+
+
+def comm_init(rank, n_ranks, unique_id):
+    check(lib().s35_comm_init(rank, n_ranks, unique_id))
+
+
+def comm_finalize():
+    lib().s35_comm_finalize()
+
+
+def comm_thread_group(n_ranks):
+    """ranks as threads of this process sharing one GPU (single-GPU tests of the partitioned path)"""
+    check(lib().s35_comm_thread_group(n_ranks))
+
+
+def comm_thread_bind(rank):
+    check(lib().s35_comm_thread_bind(rank))
 
 
 class Ctx:

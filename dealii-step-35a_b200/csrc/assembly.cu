@@ -293,13 +293,13 @@ void AdvectionAssembler::create(int dim_, int32_t n_cells_, const double *h_vert
     list[fill[h_color[c]]++] = c;
   // verify the colouring: no DoF may appear twice within one colour
   {
-    std::vector<int32_t> last_color(P.n_rows, -1);
+    std::vector<int32_t> last_color(P.n_cols, -1);
     for (int col = 0; col < n_colors; ++col)
       for (int32_t k = color_offset[col]; k < color_offset[col + 1]; ++k)
         for (int i = 0; i < dpc; ++i)
           {
             const int32_t d = h_cell_dofs[(size_t)list[k] * dpc + i];
-            S35_REQUIRE(d >= 0 && d < P.n_rows, "assembler: cell DoF index out of range");
+            S35_REQUIRE(d >= 0 && d < P.n_cols, "assembler: cell DoF index out of range");
             S35_REQUIRE(last_color[d] != col, "assembler: two cells of one colour share a DoF");
             last_color[d] = col;
           }
@@ -319,6 +319,13 @@ void AdvectionAssembler::create(int dim_, int32_t n_cells_, const double *h_vert
       for (int i = 0; i < dpc; ++i)
         {
           const int32_t r = cd[i];
+          if (r >= P.n_rows)
+            {
+              // a ghost row: its owner assembles it
+              for (int j = 0; j < dpc; ++j)
+                sl[i * dpc + j] = -1;
+              continue;
+            }
           const int32_t *b = P.h_col.data() + P.h_rowptr[r], *e = P.h_col.data() + P.h_rowptr[r + 1];
           for (int j = 0; j < dpc; ++j)
             {
@@ -396,11 +403,11 @@ double AdvectionAssembler::flops() const
 void CondensePlan::create(const DevMatrix &P, int32_t n, const int32_t *h_dofs, const double *h_values, cudaStream_t s)
 {
   n_constrained = n;
-  std::vector<double> g(P.n_rows, 0.0);
-  std::vector<char> mask(P.n_rows, 0);
+  std::vector<double> g(P.n_cols, 0.0);
+  std::vector<char> mask(P.n_cols, 0);
   for (int32_t i = 0; i < n; ++i)
     {
-      S35_REQUIRE(h_dofs[i] >= 0 && h_dofs[i] < P.n_rows, "condense: constrained DoF out of range");
+      S35_REQUIRE(h_dofs[i] >= 0 && h_dofs[i] < P.n_cols, "condense: constrained DoF out of range");
       mask[h_dofs[i]] = 1;
       g[h_dofs[i]] = h_values ? h_values[i] : 0.0;
     }
@@ -409,6 +416,13 @@ void CondensePlan::create(const DevMatrix &P, int32_t n, const int32_t *h_dofs, 
   for (int32_t i = 0; i < n; ++i)
     vals[i] = g[h_dofs[i]];
   values.upload(vals, s);
+  // constrained rows this rank owns (ghost DoFs only appear as columns)
+  std::vector<int32_t> own_rows;
+  for (int32_t i = 0; i < n; ++i)
+    if (h_dofs[i] < P.n_rows)
+      own_rows.push_back(h_dofs[i]);
+  n_row_dofs = (int32_t)own_rows.size();
+  row_dofs.upload(own_rows, s);
   std::vector<int32_t> rows, ptr(1, 0), pos;
   std::vector<double> lval;
   for (int32_t r = 0; r < P.n_rows; ++r)
@@ -441,8 +455,8 @@ void CondensePlan::condense(const DevMatrix &P, double *vals, double *rhs, const
   if (n_lift_rows)
     S35_LAUNCH(k_condense_lift, (n_lift_rows + 127) / 128, 128, 0, s, n_lift_rows, lift_row.ptr, lift_ptr.ptr, lift_pos.ptr,
                lift_val.ptr, vals, rhs);
-  if (n_constrained)
-    S35_LAUNCH(k_condense_rows, (n_constrained + 127) / 128, 128, 0, s, n_constrained, dofs.ptr, P.rowptr.ptr, P.diag.ptr, vals,
+  if (n_row_dofs)
+    S35_LAUNCH(k_condense_rows, (n_row_dofs + 127) / 128, 128, 0, s, n_row_dofs, row_dofs.ptr, P.rowptr.ptr, P.diag.ptr, vals,
                rhs, avg_diag);
 }
 

@@ -42,7 +42,9 @@ struct AdvectionAssembler
 struct CondensePlan
 {
   int32_t n_constrained = 0;
-  DevBuf<int32_t> dofs;     // constrained DoFs (ascending)
+  DevBuf<int32_t> dofs;     // constrained DoFs (ascending; on a partition: owned and ghost ones)
+  int32_t n_row_dofs = 0;
+  DevBuf<int32_t> row_dofs; // those of them that are rows of this rank's matrix
   DevBuf<double> values;    // their inhomogeneities
   // unconstrained rows that couple to a constrained column
   int32_t n_lift_rows = 0;

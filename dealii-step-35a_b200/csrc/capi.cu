@@ -257,7 +257,7 @@ s35_status s35_gmres(const s35_matrix *A, s35_ilu *prec, double *x, const double
     cudaStream_t s = A->stream;
     const int32_t n = A->m.n_rows;
     GmresSolver solver;
-    solver.init(n, krylov_size, s);
+    solver.init(n, n, krylov_size, s);
     Staged dx(x, n, s), db(b, n, s);
     s35_solver_stats st = {};
     const bool ok = solver.solve(A->m, A->m.val, prec->p, dx.d, db.d, tolerance, max_iterations, st);
@@ -278,7 +278,7 @@ s35_status s35_cg(const s35_matrix *A, s35_ilu *prec, double *x, const double *b
     cudaStream_t s = A->stream;
     const int32_t n = A->m.n_rows;
     CgSolver solver;
-    solver.init(n, s);
+    solver.init(n, n, s);
     Staged dx(x, n, s), db(b, n, s);
     s35_solver_stats st = {};
     const bool ok = solver.solve(A->m, A->m.val, prec ? &prec->p : nullptr, dx.d, db.d, tolerance, max_iterations, st);
@@ -327,6 +327,41 @@ s35_status s35_vec_add_and_dot(int64_t n, double a, const double *x, double *y, 
     vec_add_and_dot(dr.d, dy.d, DScal(a), dx.d, w == y ? dy.d.ptr : dw.d.ptr, n, kSum, ws, 0);
     dy.back(y, 0);
     dr.back(result, 0);
+  });
+}
+
+/* ---------------- communicator of the partitioned path ---------------- */
+
+s35_status s35_comm_unique_id(unsigned char id[128])
+{
+  return guarded([&] {
+    S35_REQUIRE(id != nullptr, "comm_unique_id: null argument");
+    require_device();
+    comm_unique_id(id);
+  });
+}
+
+s35_status s35_comm_init(int32_t rank, int32_t n_ranks, const unsigned char unique_id[128])
+{
+  return guarded([&] {
+    S35_REQUIRE(unique_id != nullptr, "comm_init: null argument");
+    require_device();
+    comm_init(rank, n_ranks, unique_id);
+  });
+}
+
+void s35_comm_finalize(void) { comm_finalize(); }
+
+s35_status s35_comm_thread_group(int32_t n_ranks)
+{
+  return guarded([&] { comm_thread_group(n_ranks); });
+}
+
+s35_status s35_comm_thread_bind(int32_t rank)
+{
+  return guarded([&] {
+    require_device();
+    comm_thread_bind(rank);
   });
 }
 

@@ -1,0 +1,283 @@
+#include "comm.cuh"
+
+#include <dlfcn.h>
+#include <nccl.h> // types only; the library is opened with dlopen
+
+#include <condition_variable>
+#include <cstring>
+#include <memory>
+#include <mutex>
+
+namespace s35 {
+
+namespace {
+
+__global__ void k_pack(double *__restrict__ out, const double *__restrict__ x, const int32_t *__restrict__ idx, int32_t n)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    out[i] = x[idx[i]];
+}
+
+__global__ void k_scalar_sqrt(double *x) { *x = sqrt(*x); }
+__global__ void k_scalar_scale(double *x, double f) { *x *= f; }
+
+// ------------------------------------------------------------------------------------------------ NCCL
+struct NcclApi
+{
+  void *handle = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+
+  void load()
+  {
+    if (handle)
+      return;
+    // a process that has already loaded NCCL (e.g. through torch) gets that copy
+    handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!handle)
+      handle = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!handle)
+      throw Error(S35_ERR_CUDA, std::string("cannot load libnccl: ") + dlerror());
+    auto sym = [&](const char *name) {
+      void *p = dlsym(handle, name);
+      if (!p)
+        throw Error(S35_ERR_CUDA, std::string("libnccl lacks ") + name);
+      return p;
+    };
+    GetUniqueId = (decltype(GetUniqueId))sym("ncclGetUniqueId");
+    CommInitRank = (decltype(CommInitRank))sym("ncclCommInitRank");
+    CommDestroy = (decltype(CommDestroy))sym("ncclCommDestroy");
+    AllReduce = (decltype(AllReduce))sym("ncclAllReduce");
+    Send = (decltype(Send))sym("ncclSend");
+    Recv = (decltype(Recv))sym("ncclRecv");
+    GroupStart = (decltype(GroupStart))sym("ncclGroupStart");
+    GroupEnd = (decltype(GroupEnd))sym("ncclGroupEnd");
+    GetErrorString = (decltype(GetErrorString))sym("ncclGetErrorString");
+  }
+  void check(ncclResult_t r, const char *what)
+  {
+    if (r != ncclSuccess)
+      throw Error(S35_ERR_CUDA, std::string("NCCL error in ") + what + ": " + (GetErrorString ? GetErrorString(r) : "?"));
+  }
+};
+
+NcclApi g_nccl;
+
+struct NcclComm : Comm
+{
+  ncclComm_t comm = nullptr;
+  ~NcclComm() override
+  {
+    if (comm)
+      g_nccl.CommDestroy(comm);
+  }
+  void allreduce_sum(double *buf, int count, cudaStream_t s) override
+  {
+    g_nccl.check(g_nccl.AllReduce(buf, buf, (size_t)count, ncclDouble, ncclSum, comm, s), "ncclAllReduce");
+  }
+  void exchange(HaloDev &h, double *x, cudaStream_t s) override
+  {
+    if (h.empty())
+      return;
+    const int32_t n_send = h.send_ptr.back();
+    if (n_send)
+      S35_LAUNCH(k_pack, (n_send + 255) / 256, 256, 0, s, h.send_buf.ptr, x, h.send_idx.ptr, n_send);
+    g_nccl.check(g_nccl.GroupStart(), "ncclGroupStart");
+    for (size_t q = 0; q < h.neighbor_rank.size(); ++q)
+      {
+        const int32_t ns = h.send_ptr[q + 1] - h.send_ptr[q], nr = h.recv_ptr[q + 1] - h.recv_ptr[q];
+        if (ns)
+          g_nccl.check(g_nccl.Send(h.send_buf.ptr + h.send_ptr[q], (size_t)ns, ncclDouble, h.neighbor_rank[q], comm, s), "ncclSend");
+        if (nr)
+          g_nccl.check(g_nccl.Recv(x + h.n_owned + h.recv_ptr[q], (size_t)nr, ncclDouble, h.neighbor_rank[q], comm, s), "ncclRecv");
+      }
+    g_nccl.check(g_nccl.GroupEnd(), "ncclGroupEnd");
+  }
+};
+
+std::unique_ptr<Comm> g_process_comm;
+
+// ------------------------------------------------------------------------ ranks as threads of one process
+// N ranks as N host threads sharing ONE GPU: the same partitioned code path without NCCL (which refuses two
+// ranks on one device).  Used by the single-GPU tests of the multi-rank path.  The exchange is a gather from
+// the peer's vector, the reduction a sum over the peers' buffers in rank order (identical on all ranks).
+struct ThreadGroup
+{
+  int n = 0;
+  std::mutex m;
+  std::condition_variable cv;
+  int waiting = 0;
+  long generation = 0;
+  std::vector<double *> ptr;
+  std::vector<HaloDev *> halo;
+  void barrier()
+  {
+    std::unique_lock<std::mutex> lock(m);
+    const long gen = generation;
+    if (++waiting == n)
+      {
+        waiting = 0;
+        ++generation;
+        cv.notify_all();
+      }
+    else
+      cv.wait(lock, [&] { return gen != generation; });
+  }
+};
+
+struct PeerPtrs
+{
+  const double *p[16];
+};
+
+__global__ void k_sum_peers(double *out, PeerPtrs peers, int n_ranks, int count)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < count)
+    {
+      double s = 0.0;
+      for (int r = 0; r < n_ranks; ++r)
+        s += peers.p[r][i];
+      out[i] = s;
+    }
+}
+
+__global__ void k_gather_from_peer(double *__restrict__ dst, const double *__restrict__ peer_x,
+                                   const int32_t *__restrict__ peer_send_idx, int32_t n)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    dst[i] = peer_x[peer_send_idx[i]];
+}
+
+struct ThreadComm : Comm
+{
+  std::shared_ptr<ThreadGroup> g;
+  DevBuf<double> tmp;
+  void allreduce_sum(double *buf, int count, cudaStream_t s) override
+  {
+    S35_REQUIRE(count <= 64, "thread communicator: reduction too long");
+    if (tmp.n < 64)
+      tmp.alloc(64);
+    S35_CUDA(cudaStreamSynchronize(s));
+    g->ptr[rank] = buf;
+    g->barrier();
+    PeerPtrs peers;
+    for (int r = 0; r < n_ranks; ++r)
+      peers.p[r] = g->ptr[r];
+    S35_LAUNCH(k_sum_peers, 1, 64, 0, s, tmp.ptr, peers, n_ranks, count);
+    S35_CUDA(cudaStreamSynchronize(s));
+    g->barrier(); // every rank has read every buffer
+    S35_CUDA(cudaMemcpyAsync(buf, tmp.ptr, count * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  }
+  void exchange(HaloDev &h, double *x, cudaStream_t s) override
+  {
+    S35_CUDA(cudaStreamSynchronize(s));
+    g->ptr[rank] = x;
+    g->halo[rank] = &h;
+    g->barrier();
+    for (size_t q = 0; q < h.neighbor_rank.size(); ++q)
+      {
+        const int peer = h.neighbor_rank[q];
+        const int32_t nr = h.recv_ptr[q + 1] - h.recv_ptr[q];
+        if (!nr)
+          continue;
+        HaloDev &ph = *g->halo[peer];
+        size_t me = 0;
+        while (me < ph.neighbor_rank.size() && ph.neighbor_rank[me] != rank)
+          ++me;
+        S35_REQUIRE(me < ph.neighbor_rank.size() && ph.send_ptr[me + 1] - ph.send_ptr[me] == nr,
+                    "thread communicator: halo plans of two ranks do not match");
+        S35_LAUNCH(k_gather_from_peer, (nr + 255) / 256, 256, 0, s, x + h.n_owned + h.recv_ptr[q], g->ptr[peer],
+                   ph.send_idx.ptr + ph.send_ptr[me], nr);
+      }
+    S35_CUDA(cudaStreamSynchronize(s));
+    g->barrier(); // nobody overwrites owned values before every neighbour has read them
+  }
+};
+
+std::shared_ptr<ThreadGroup> g_thread_group;
+thread_local std::unique_ptr<ThreadComm> t_thread_comm;
+
+} // namespace
+
+void HaloDev::create(const s35_halo &h, int32_t n_owned_, int32_t n_local_, cudaStream_t s)
+{
+  n_owned = n_owned_;
+  n_local = n_local_;
+  neighbor_rank.assign(h.neighbor_rank, h.neighbor_rank + h.n_neighbors);
+  send_ptr.assign(h.send_ptr, h.send_ptr + h.n_neighbors + 1);
+  recv_ptr.assign(h.recv_ptr, h.recv_ptr + h.n_neighbors + 1);
+  S35_REQUIRE(recv_ptr.back() == n_local - n_owned, "halo: the receive segments do not cover the ghost DoFs");
+  for (int32_t i = 0; i < send_ptr.back(); ++i)
+    S35_REQUIRE(h.send_idx[i] >= 0 && h.send_idx[i] < n_owned, "halo: send index is not an owned DoF");
+  send_idx.upload(h.send_idx, (size_t)send_ptr.back(), s);
+  send_buf.alloc((size_t)std::max<int32_t>(send_ptr.back(), 1));
+}
+
+Comm *process_comm()
+{
+  if (t_thread_comm)
+    return t_thread_comm.get();
+  return g_process_comm.get();
+}
+
+void comm_unique_id(unsigned char id[128])
+{
+  g_nccl.load();
+  ncclUniqueId uid;
+  g_nccl.check(g_nccl.GetUniqueId(&uid), "ncclGetUniqueId");
+  static_assert(sizeof(uid) == 128, "ncclUniqueId is expected to be 128 bytes");
+  std::memcpy(id, &uid, 128);
+}
+
+void comm_init(int rank, int n_ranks, const unsigned char id[128])
+{
+  S35_REQUIRE(n_ranks >= 1 && rank >= 0 && rank < n_ranks, "comm_init: bad rank / n_ranks");
+  g_nccl.load();
+  std::unique_ptr<NcclComm> c(new NcclComm);
+  c->rank = rank;
+  c->n_ranks = n_ranks;
+  ncclUniqueId uid;
+  std::memcpy(&uid, id, 128);
+  g_nccl.check(g_nccl.CommInitRank(&c->comm, n_ranks, uid, rank), "ncclCommInitRank");
+  g_process_comm = std::move(c);
+}
+
+void comm_finalize()
+{
+  g_process_comm.reset();
+  t_thread_comm.reset();
+}
+
+void comm_thread_group(int n_ranks)
+{
+  S35_REQUIRE(n_ranks >= 1 && n_ranks <= 16, "thread communicator: 1..16 ranks");
+  std::shared_ptr<ThreadGroup> g(new ThreadGroup);
+  g->n = n_ranks;
+  g->ptr.assign(n_ranks, nullptr);
+  g->halo.assign(n_ranks, nullptr);
+  g_thread_group = g;
+}
+
+void comm_thread_bind(int rank)
+{
+  S35_REQUIRE(g_thread_group && rank >= 0 && rank < g_thread_group->n, "thread communicator: no group or bad rank");
+  t_thread_comm.reset(new ThreadComm);
+  t_thread_comm->g = g_thread_group;
+  t_thread_comm->rank = rank;
+  t_thread_comm->n_ranks = g_thread_group->n;
+}
+
+void scalar_sqrt(double *x, cudaStream_t s) { S35_LAUNCH(k_scalar_sqrt, 1, 1, 0, s, x); }
+void scalar_scale(double *x, double f, cudaStream_t s) { S35_LAUNCH(k_scalar_scale, 1, 1, 0, s, x, f); }
+
+} // namespace s35

@@ -62,6 +62,19 @@ Ctx::Ctx(const s35_problem &p)
   n_cells = p.n_cells;
   nv = p.n_vel;
   np = p.n_pres;
+  const s35_dist *D = p.dist;
+  nv_own = D ? D->n_vel_owned : nv;
+  np_own = D ? D->n_pres_owned : np;
+  nv_global = D ? D->n_vel_global : nv;
+  np_global = D ? D->n_pres_global : np;
+  S35_REQUIRE(nv_own > 0 && nv_own <= nv && np_own > 0 && np_own <= np, "problem: bad owned DoF counts");
+  if (D && D->n_ranks > 1)
+    {
+      comm = process_comm();
+      if (!comm)
+        throw Error(S35_ERR_INVALID, "a partitioned problem needs a communicator: call s35_comm_init first");
+      S35_REQUIRE(comm->n_ranks == D->n_ranks && comm->rank == D->rank, "problem: rank / n_ranks differ from the communicator's");
+    }
   dt = p.dt;
   reynolds = p.reynolds;
   eps = p.vel_eps;
@@ -77,24 +90,41 @@ Ctx::Ctx(const s35_problem &p)
   S35_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
   cudaStream_t s = stream;
 
-  vel_adv.create(nv, nv, p.velc_rowptr, p.velc_col, nullptr, s);
-  vel_mass.create(nv, nv, p.velm_rowptr, p.velm_col, p.velm_val, s);
+  // rows: owned DoFs; columns: all local DoFs (owned, then ghosts)
+  vel_adv.create(nv_own, nv, p.velc_rowptr, p.velc_col, nullptr, s);
+  vel_mass.create(nv_own, nv, p.velm_rowptr, p.velm_col, p.velm_val, s);
   S35_REQUIRE(p.grad_val[0] != nullptr, "problem: null gradient operator");
-  grad.create(nv, np, p.grad_rowptr, p.grad_col, p.grad_val[0], s);
-  gradT = &grad.transpose(s);
+  grad.create(nv_own, np, p.grad_rowptr, p.grad_col, p.grad_val[0], s);
+  if (D)
+    {
+      // the rows of pres_Diff^T for the owned pressure DoFs come with the partition
+      S35_REQUIRE(D->gradT_rowptr && D->gradT_col, "problem: the partition lacks the transposed gradient rows");
+      gradT_own.create(np_own, nv, D->gradT_rowptr, D->gradT_col, nullptr, s);
+      gradT = &gradT_own;
+    }
+  else
+    gradT = &grad.transpose(s);
   for (int d = 0; d < dim; ++d)
     {
       S35_REQUIRE(p.grad_val[d] != nullptr, "problem: null gradient operator");
       it_val[d].alloc(vel_adv.nnz);
       grad_val[d].upload(p.grad_val[d], grad.nnz, s);
-      gradT_val[d].alloc(grad.nnz);
-      gather_values(gradT_val[d], grad_val[d], grad.transposed->perm, grad.nnz, s);
+      if (D)
+        {
+          S35_REQUIRE(D->gradT_val[d] != nullptr, "problem: the partition lacks the transposed gradient values");
+          gradT_val[d].upload(D->gradT_val[d], gradT_own.nnz, s);
+        }
+      else
+        {
+          gradT_val[d].alloc(grad.nnz);
+          gather_values(gradT_val[d], grad_val[d], grad.transposed->perm, grad.nnz, s);
+        }
     }
-  plap.create(np, np, p.plap_rowptr, p.plap_col, p.plap_val, s);
-  pmass.create(np, np, p.pmass_rowptr, p.pmass_col, p.pmass_val, s);
+  plap.create(np_own, np, p.plap_rowptr, p.plap_col, p.plap_val, s);
+  pmass.create(np_own, np, p.pmass_rowptr, p.pmass_col, p.pmass_val, s);
   {
-    std::vector<double> inv(np);
-    for (int32_t r = 0; r < np; ++r)
+    std::vector<double> inv(np_own);
+    for (int32_t r = 0; r < np_own; ++r)
       {
         int32_t pos = -1;
         for (int32_t k = p.pmass_rowptr[r]; k < p.pmass_rowptr[r + 1]; ++k)
@@ -143,24 +173,56 @@ Ctx::Ctx(const s35_problem &p)
   }
 
   // preconditioners (pressure: built once, step-35a.cc:1070-1074) and solvers
+  // On a partition the preconditioner is the ILU(0) of the rank's diagonal block (owned rows x owned columns):
+  // couplings to ghost columns are dropped.  Ghost columns sort last, so the block is a prefix of every row.
+  auto make_block = [&](const DevMatrix &A, int32_t n_own, DevMatrix &blk, DevBuf<int32_t> &src) {
+    std::vector<int32_t> rp(n_own + 1, 0), cl, from;
+    for (int32_t r = 0; r < n_own; ++r)
+      {
+        for (int32_t k = A.h_rowptr[r]; k < A.h_rowptr[r + 1] && A.h_col[k] < n_own; ++k)
+          {
+            cl.push_back(A.h_col[k]);
+            from.push_back(k);
+          }
+        rp[r + 1] = (int32_t)cl.size();
+      }
+    blk.create(n_own, n_own, rp.data(), cl.data(), nullptr, s);
+    src.upload(from, s);
+  };
+  use_blocks = D != nullptr && (nv_own < nv || np_own < np);
+  if (use_blocks)
+    {
+      make_block(vel_adv, nv_own, vel_blk, vel_blk_src);
+      make_block(plap, np_own, plap_blk, plap_blk_src);
+      for (int d = 0; d < dim; ++d)
+        blk_val[d].alloc(vel_blk.nnz);
+      gather_values(plap_blk.val, plap.val, plap_blk_src, plap_blk.nnz, s);
+      vel_halo.create(D->vel_halo, nv_own, nv, s);
+      pres_halo.create(D->pres_halo, np_own, np, s);
+    }
   for (int d = 0; d < dim; ++d)
-    prec_vel[d].create(vel_adv, s);
-  prec_pres.create(plap, s);
-  prec_pres.factor(plap.val, diag_strength, s);
+    prec_vel[d].create(use_blocks ? vel_blk : vel_adv, s);
+  prec_pres.create(use_blocks ? plap_blk : plap, s);
+  prec_pres.factor(use_blocks ? plap_blk.val : plap.val, diag_strength, s);
   prec_pres.check_pivots(s);
-  concurrent_components = true;
+  // one communicator cannot serve several streams at once: the components take turns on a partition
+  concurrent_components = comm == nullptr;
   if (const char *t = std::getenv("S35_CONCURRENT_COMPONENTS"))
-    concurrent_components = std::atoi(t) != 0;
+    concurrent_components = concurrent_components && std::atoi(t) != 0;
   S35_CUDA(cudaEventCreateWithFlags(&fork_event, cudaEventDisableTiming));
   for (int d = 0; d < dim; ++d)
     {
       S35_CUDA(cudaStreamCreateWithFlags(&comp_stream[d], cudaStreamNonBlocking));
       S35_CUDA(cudaEventCreateWithFlags(&join_event[d], cudaEventDisableTiming));
-      gmres[d].init(nv, krylov, concurrent_components ? comp_stream[d] : s);
+      gmres[d].init(nv_own, nv, krylov, concurrent_components ? comp_stream[d] : s);
+      gmres[d].dist = DistLink{comm, use_blocks ? &vel_halo : nullptr};
       ws_comp[d].init(concurrent_components ? comp_stream[d] : s);
       S35_CUDA(cudaStreamSynchronize(comp_stream[d]));
     }
-  cg.init(np, s);
+  cg.init(np_own, np, s);
+  cg.dist = DistLink{comm, use_blocks ? &pres_halo : nullptr};
+  vel_link = DistLink{comm, use_blocks ? &vel_halo : nullptr};
+  pres_link = cg.dist;
   ws.init(s);
   scal.alloc(8);
   scal.zero(s);
@@ -296,10 +358,17 @@ void Ctx::solve_component(int d, bool reinit_prec, cudaStream_t s)
   flow[d].condense(vel_adv, it_val[d], force[d], scal.ptr + 0, s);
   if (reinit_prec)
     {
-      prec_vel[d].factor(it_val[d], diag_strength, s);
+      const double *factor_input = it_val[d];
+      if (use_blocks)
+        {
+          gather_values(blk_val[d], it_val[d], vel_blk_src, vel_blk.nnz, s);
+          factor_input = blk_val[d];
+        }
+      prec_vel[d].factor(factor_input, diag_strength, s);
       prec_vel[d].check_pivots(s);
     }
-  vec_dot(scal.ptr + 1 + d, force[d], force[d], nv, kSqrt, ws_comp[d], s);
+  vec_dot(scal.ptr + 1 + d, force[d], force[d], nv_own, vel_link.local_post(true), ws_comp[d], s);
+  vel_link.finish_sums(scal.ptr + 1 + d, 1, true, s);
   S35_CUDA(cudaMemcpyAsync(scal_host.ptr + 1 + d, scal.ptr + 1 + d, sizeof(double), cudaMemcpyDeviceToHost, s));
   S35_CUDA(cudaStreamSynchronize(s));
   const double tol = eps * scal_host.ptr[1 + d];
@@ -310,6 +379,7 @@ void Ctx::solve_component(int d, bool reinit_prec, cudaStream_t s)
                                           std::to_string(stats_vel[d].final_residual));
   vec_scatter_set(u_n[d], flow[d].dofs, flow[d].values, flow[d].n_constrained, s); // flow constraints distribute
   vec_scatter_set(u_n[d], wall_dofs, nullptr, n_wall, s);                          // wall constraints distribute
+  vel_link.refresh_ghosts(u_n[d], s);
 }
 
 // step-35a.cc:1268-1338.  The reference runs the dim components as concurrent tasks (Threads::new_task,
@@ -345,6 +415,13 @@ void Ctx::diffusion_step(bool reinit_prec)
   {
     const size_t sec = begin_section("solve_diffusion_component");
     diag_abs_mean(vel_adv, vel_adv.val, scal.ptr + 0, ws, s);
+    if (comm)
+      {
+        // mean over ALL velocity DoFs: local mean -> local sum -> sum over ranks -> / global count
+        scalar_scale(scal.ptr + 0, (double)nv_own, s);
+        comm->allreduce_sum(scal.ptr + 0, 1, s);
+        scalar_scale(scal.ptr + 0, 1.0 / (double)nv_global, s);
+      }
     if (!concurrent_components)
       {
         try
@@ -413,12 +490,14 @@ void Ctx::projection_step()
   }
   {
     const size_t sec = begin_section("projection_step_solve");
-    vec_dot(scal.ptr + 4, pres_tmp, pres_tmp, np, kSqrt, ws, s); // the tolerance uses the norm before condense
+    vec_dot(scal.ptr + 4, pres_tmp, pres_tmp, np_own, pres_link.local_post(true), ws, s); // norm BEFORE condense
+    pres_link.finish_sums(scal.ptr + 4, 1, true, s);
     S35_CUDA(cudaMemcpyAsync(scal_host.ptr + 4, scal.ptr + 4, sizeof(double), cudaMemcpyDeviceToHost, s));
     vec_scatter_set(pres_tmp, proj_dofs, nullptr, n_proj, s); // projection_constraints.condense(pres_tmp)
     S35_CUDA(cudaStreamSynchronize(s));
     const double tol = eps * scal_host.ptr[4];
     const bool ok = cg.solve(plap, plap.val, &prec_pres, phi_n, pres_tmp, tol, max_its, stats_proj);
+    pres_link.refresh_ghosts(phi_n, s);
     if (!ok)
       {
         end_section(sec);
@@ -448,13 +527,15 @@ void Ctx::update_pressure()
     vec_lincomb(pres_n, DScal(1.0), pres_n, DScal(1.0), phi_n, np, s);
   else
     {
-      vec_dot(scal.ptr + 5, pres_tmp, pres_tmp, np, kSqrt, ws, s);
+      vec_dot(scal.ptr + 5, pres_tmp, pres_tmp, np_own, pres_link.local_post(true), ws, s);
+      pres_link.finish_sums(scal.ptr + 5, 1, true, s);
       S35_CUDA(cudaMemcpyAsync(scal_host.ptr + 5, scal.ptr + 5, sizeof(double), cudaMemcpyDeviceToHost, s));
       p_work.zero(s);
       S35_CUDA(cudaStreamSynchronize(s));
       const double tol = 1e-14 * scal_host.ptr[5];
       // a stagnating residual recurrence near machine precision is not a failure of the time step
       cg.solve(pmass, pmass.val, nullptr, p_work, pres_tmp, tol, 200, stats_mass, pmass_inv_diag);
+      pres_link.refresh_ghosts(p_work, s);
       // pres_n = 1/Re * M^-1 pres_tmp + pres_n_minus_1 + phi_n
       vec_lincomb3(pres_n, DScal(1.0 / reynolds), p_work, DScal(1.0), pres_nm1, DScal(1.0), phi_n, np, s);
     }

@@ -19,7 +19,10 @@ struct SectionTimer
 struct Ctx
 {
   int dim = 0;
-  int32_t n_cells = 0, nv = 0, np = 0;
+  int32_t n_cells = 0;
+  int32_t nv = 0, np = 0;         // local DoFs: owned, then ghosts (all DoFs on a single GPU)
+  int32_t nv_own = 0, np_own = 0; // owned DoFs = matrix rows on this rank
+  int64_t nv_global = 0, np_global = 0;
   int64_t n_vertices = 0;
   double dt = 0, reynolds = 0, eps = 0, diag_strength = 0;
   int max_its = 0, krylov = 0, update_prec = 0;
@@ -33,7 +36,16 @@ struct Ctx
   DevMatrix vel_mass;             // unconstrained pattern
   DevMatrix grad;                 // pres_Diff pattern; values of component 0
   DevBuf<double> grad_val[3];     // pres_Diff[d] values
-  const DevMatrix *gradT = nullptr; // transposed pattern (owned by grad)
+  const DevMatrix *gradT = nullptr; // transposed pattern (owned by grad, or gradT_own on a partition)
+  DevMatrix gradT_own;
+  // partition: communicator, ghost exchange plans, diagonal blocks for the ILU(0) factors
+  Comm *comm = nullptr;
+  HaloDev vel_halo, pres_halo;
+  DistLink vel_link, pres_link;
+  bool use_blocks = false;
+  DevMatrix vel_blk, plap_blk;
+  DevBuf<int32_t> vel_blk_src, plap_blk_src;
+  DevBuf<double> blk_val[3];
   DevBuf<double> gradT_val[3];
   DevMatrix plap, pmass;
   DevBuf<double> pmass_inv_diag;

@@ -5,14 +5,16 @@
 
 namespace s35 {
 
-void GmresSolver::init(int32_t n_, int krylov_size, cudaStream_t s)
+void GmresSolver::init(int32_t n_owned, int32_t n_local_, int krylov_size, cudaStream_t s)
 {
   S35_REQUIRE(krylov_size >= 3, "GMRES: Krylov_size must be at least 3 (two of the vectors are work space)");
   S35_REQUIRE(krylov_size <= 34, "GMRES: Krylov_size above 34 is not supported by this build");
-  n = n_;
+  n = n_owned;
+  n_local = n_local_;
   n_tmp = krylov_size;
-  stride = ((int64_t)n + 1) & ~(int64_t)1;
+  stride = ((int64_t)n_local + 1) & ~(int64_t)1;
   tmp.alloc((size_t)stride * n_tmp);
+  tmp.zero(s);
   h_dev.alloc(n_tmp + 4);
   h_host.alloc(n_tmp + 4);
   ws.init(s);
@@ -28,6 +30,18 @@ bool GmresSolver::solve(const DevMatrix &P, const double *values, DevIlu &prec, 
   double *const hd = h_dev.ptr;
   double *const hh = h_host.ptr;
   const int i_norm = n_tmp, i_start = n_tmp + 1; // slots for ||vv|| and ||vv||_start
+  auto matvec = [&](double *in, double *out) {
+    dist.refresh_ghosts(in, s);
+    spmv_values(P, values, in, out, false, s);
+  };
+  auto dot = [&](double *result, const double *a, const double *c, bool take_sqrt) {
+    vec_dot(result, a, c, n, dist.local_post(take_sqrt), ws, s);
+    dist.finish_sums(result, 1, take_sqrt, s);
+  };
+  auto add_and_dot = [&](double *result, double *y, DScal a, const double *xx, const double *w, bool take_sqrt) {
+    vec_add_and_dot(result, y, a, xx, w, n, dist.local_post(take_sqrt), ws, s);
+    dist.finish_sums(result, 1, take_sqrt, s);
+  };
 
   std::vector<double> H((size_t)n_tmp * (n_tmp - 1), 0.0); // H(i,j) = H[i*(n_tmp-1)+j]
   std::vector<double> gamma(n_tmp), ci(n_tmp - 1), si(n_tmp - 1), h(n_tmp - 1);
@@ -41,14 +55,24 @@ bool GmresSolver::solve(const DevMatrix &P, const double *values, DevIlu &prec, 
   stats.initial_residual = 0.0;
   stats.tolerance = tol;
 
+  // modified Gram-Schmidt pass over the first `dim` basis vectors; coefficients at hd[0..dim), norm at hd[i_norm]
+  auto gram_schmidt_pass = [&](double *vv) {
+    dot(hd + 0, vv, vec(0), false);
+    for (unsigned i = 1; i < dim; ++i)
+      add_and_dot(hd + i, vv, DScal(hd + i - 1, -1.0), vec(i - 1), vec(i), false);
+    add_and_dot(hd + i_norm, vv, DScal(hd + dim - 1, -1.0), vec(dim - 1), vv, true);
+    S35_CUDA(cudaMemcpyAsync(hh, hd, (n_tmp + 2) * sizeof(double), cudaMemcpyDeviceToHost, s));
+    S35_CUDA(cudaStreamSynchronize(s));
+  };
+
   do
     {
       std::fill(h.begin(), h.end(), 0.0);
       // p = b - A x ; v = P^-1 p
-      spmv_values(P, values, x, p, false, s);
+      matvec(x, p);
       vec_lincomb(p, DScal(-1.0), p, DScal(1.0), b, n, s);
       prec.apply(v, p, s);
-      vec_dot(hd + i_norm, v, v, n, kSqrt, ws, s);
+      dot(hd + i_norm, v, v, true);
       S35_CUDA(cudaMemcpyAsync(hh + i_norm, hd + i_norm, sizeof(double), cudaMemcpyDeviceToHost, s));
       S35_CUDA(cudaStreamSynchronize(s));
       double rho = hh[i_norm];
@@ -65,20 +89,15 @@ bool GmresSolver::solve(const DevMatrix &P, const double *values, DevIlu &prec, 
         {
           ++accumulated;
           double *vv = vec(inner + 1);
-          spmv_values(P, values, vec(inner), p, false, s);
+          matvec(vec(inner), p);
           prec.apply(vv, p, s);
           dim = inner + 1;
 
-          // modified Gram-Schmidt (SolverGMRES::modified_gram_schmidt)
+          // SolverGMRES::modified_gram_schmidt
           const bool consider_reorthogonalize = !reorthogonalize && (inner % 5 == 4);
           if (consider_reorthogonalize)
-            vec_dot(hd + i_start, vv, vv, n, kSqrt, ws, s);
-          vec_dot(hd + 0, vv, vec(0), n, kSum, ws, s);
-          for (unsigned i = 1; i < dim; ++i)
-            vec_add_and_dot(hd + i, vv, DScal(hd + i - 1, -1.0), vec(i - 1), vec(i), n, kSum, ws, s);
-          vec_add_and_dot(hd + i_norm, vv, DScal(hd + dim - 1, -1.0), vec(dim - 1), vv, n, kSqrt, ws, s);
-          S35_CUDA(cudaMemcpyAsync(hh, hd, (n_tmp + 2) * sizeof(double), cudaMemcpyDeviceToHost, s));
-          S35_CUDA(cudaStreamSynchronize(s));
+            dot(hd + i_start, vv, vv, true);
+          gram_schmidt_pass(vv);
           for (unsigned i = 0; i < dim; ++i)
             h[i] = hh[i];
           double norm_vv = hh[i_norm];
@@ -91,12 +110,7 @@ bool GmresSolver::solve(const DevMatrix &P, const double *values, DevIlu &prec, 
           if (reorthogonalize)
             {
               // second pass, entered once loss of orthogonality has been detected; corrections add to h
-              vec_dot(hd + 0, vv, vec(0), n, kSum, ws, s);
-              for (unsigned i = 1; i < dim; ++i)
-                vec_add_and_dot(hd + i, vv, DScal(hd + i - 1, -1.0), vec(i - 1), vec(i), n, kSum, ws, s);
-              vec_add_and_dot(hd + i_norm, vv, DScal(hd + dim - 1, -1.0), vec(dim - 1), vv, n, kSqrt, ws, s);
-              S35_CUDA(cudaMemcpyAsync(hh, hd, (n_tmp + 2) * sizeof(double), cudaMemcpyDeviceToHost, s));
-              S35_CUDA(cudaStreamSynchronize(s));
+              gram_schmidt_pass(vv);
               for (unsigned i = 0; i < dim; ++i)
                 h[i] += hh[i];
               norm_vv = hh[i_norm];
@@ -145,12 +159,16 @@ bool GmresSolver::solve(const DevMatrix &P, const double *values, DevIlu &prec, 
   return state == SolverState::success;
 }
 
-void CgSolver::init(int32_t n_, cudaStream_t s)
+void CgSolver::init(int32_t n_owned, int32_t n_local_, cudaStream_t s)
 {
-  n = n_;
-  g.alloc(n);
-  d.alloc(n);
-  h.alloc(n);
+  n = n_owned;
+  n_local = n_local_;
+  g.alloc(n_local);
+  d.alloc(n_local);
+  h.alloc(n_local);
+  g.zero(s);
+  d.zero(s);
+  h.zero(s);
   scal.alloc(8);
   res_host.alloc(2);
   ws.init(s);
@@ -184,11 +202,20 @@ bool CgSolver::solve(const DevMatrix &P, const double *values, DevIlu *prec, dou
     else
       vec_copy(dst, src, n, s);
   };
+  auto matvec = [&](double *in, double *out) {
+    dist.refresh_ghosts(in, s);
+    spmv_values(P, values, in, out, false, s);
+  };
+  auto dot = [&](double *result, const double *a, const double *c) {
+    vec_dot(result, a, c, n, kSum, ws, s);
+    dist.finish_sums(result, 1, false, s);
+  };
   stats.tolerance = tol;
   int it = 0;
   // g = A x - b (for x == 0 this is exactly -b, the reference's short cut)
-  spmv_values(P, values, x, g, false, s);
-  vec_add_and_dot(sc + RES, g, DScal(-1.0), b, g, n, kSqrt, ws, s);
+  matvec(x, g);
+  vec_add_and_dot(sc + RES, g, DScal(-1.0), b, g, n, dist.local_post(true), ws, s);
+  dist.finish_sums(sc + RES, 1, true, s);
   double res = read_res();
   stats.initial_residual = res;
   SolverState state = solver_check(0, res, tol, max_iterations);
@@ -196,20 +223,21 @@ bool CgSolver::solve(const DevMatrix &P, const double *values, DevIlu *prec, dou
     {
       precondition(h, g);
       vec_lincomb(d, DScal(-1.0), h, DScal(0.0), nullptr, n, s);
-      vec_dot(sc + GH, g, h, n, kSum, ws, s);
+      dot(sc + GH, g, h);
       while (state == SolverState::iterate)
         {
           ++it;
-          spmv_values(P, values, d, h, false, s);
-          vec_dot(sc + DH, d, h, n, kSum, ws, s);
+          matvec(d, h);
+          dot(sc + DH, d, h);
           scalar_divide(sc + ALPHA, sc + GH, sc + DH, nullptr, s);
-          vec_cg_update(sc + RES, x, g, DScal(sc + ALPHA), d, h, n, ws, s);
+          vec_cg_update(sc + RES, x, g, DScal(sc + ALPHA), d, h, n, dist.local_post(true), ws, s);
+          dist.finish_sums(sc + RES, 1, true, s);
           res = read_res();
           state = solver_check(it, res, tol, max_iterations);
           if (state != SolverState::iterate)
             break;
           precondition(h, g);
-          vec_dot(sc + GHNEW, g, h, n, kSum, ws, s);
+          dot(sc + GHNEW, g, h);
           // beta = gh_new / gh_old ; gh = gh_new
           scalar_divide(sc + BETA, sc + GHNEW, sc + GH, sc + GH, s);
           vec_lincomb(d, DScal(sc + BETA), d, DScal(-1.0), h, n, s);

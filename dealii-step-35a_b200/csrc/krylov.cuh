@@ -4,7 +4,12 @@
 // Vectors live on the device; the Hessenberg / Givens bookkeeping of GMRES
 // (a handful of scalars per iteration) is done on the host exactly as
 // deal.II does it, after one read-back per iteration.
+//
+// On a mesh-partitioned problem (`dist` set) a vector holds the rank's owned entries followed by its ghost
+// entries: vector operations and dot products run over the owned part, every dot product is completed by a
+// sum over the ranks, and the ghost entries of a mat-vec's input are refreshed right before it.
 #pragma once
+#include "comm.cuh"
 #include "ilu.cuh"
 #include "vecops.cuh"
 
@@ -26,9 +31,36 @@ inline SolverState solver_check(int step, double value, double tol, int max_step
   return SolverState::iterate;
 }
 
+// how a solver reaches the other ranks; both null on a single GPU
+struct DistLink
+{
+  Comm *comm = nullptr;
+  HaloDev *halo = nullptr;
+  // x's ghost entries <- owners' values
+  void refresh_ghosts(double *x, cudaStream_t s) const
+  {
+    if (comm && halo)
+      comm->exchange(*halo, x, s);
+  }
+  // completes `count` local sums at `result` (device) and applies the square root if asked
+  void finish_sums(double *result, int count, bool take_sqrt, cudaStream_t s) const
+  {
+    if (comm)
+      {
+        comm->allreduce_sum(result, count, s);
+        if (take_sqrt)
+          for (int i = 0; i < count; ++i)
+            scalar_sqrt(result + i, s);
+      }
+  }
+  // the reduction kernels apply the square root themselves only when no cross-rank sum follows
+  ReducePost local_post(bool take_sqrt) const { return (take_sqrt && !comm) ? kSqrt : kSum; }
+};
+
 struct GmresSolver
 {
-  int32_t n = 0;
+  int32_t n = 0;          // owned entries: length of vector operations
+  int32_t n_local = 0;    // owned + ghost entries: length of a stored vector
   int n_tmp = 0;          // AdditionalData::max_n_tmp_vectors (= Krylov_size)
   int64_t stride = 0;     // distance between basis vectors
   DevBuf<double> tmp;     // n_tmp vectors
@@ -36,8 +68,9 @@ struct GmresSolver
   PinnedBuf<double> h_host;
   ReduceWs ws;
   cudaStream_t stream = 0;
+  DistLink dist;
 
-  void init(int32_t n, int krylov_size, cudaStream_t s);
+  void init(int32_t n_owned, int32_t n_local, int krylov_size, cudaStream_t s);
   // returns false on SolverControl failure (iteration limit / NaN); x holds the last iterate either way
   bool solve(const DevMatrix &pattern, const double *values, DevIlu &prec, double *x, const double *b, double tol,
              int max_iterations, s35_solver_stats &stats);
@@ -45,14 +78,15 @@ struct GmresSolver
 
 struct CgSolver
 {
-  int32_t n = 0;
+  int32_t n = 0, n_local = 0;
   DevBuf<double> g, d, h;
   DevBuf<double> scal;    // [0] d.h  [1] alpha  [2] gh  [3] res  [4] gh_new  [5] beta
   PinnedBuf<double> res_host;
   ReduceWs ws;
   cudaStream_t stream = 0;
+  DistLink dist;
 
-  void init(int32_t n, cudaStream_t s);
+  void init(int32_t n_owned, int32_t n_local, cudaStream_t s);
   // prec may be null; then inv_diag (Jacobi, h = inv_diag .* g) is used if given, else PreconditionIdentity
   bool solve(const DevMatrix &pattern, const double *values, DevIlu *prec, double *x, const double *b, double tol,
              int max_iterations, s35_solver_stats &stats, const double *inv_diag = nullptr);

@@ -90,7 +90,7 @@ void DevMatrix::create(int32_t nr, int32_t nc, const int32_t *h_rp, const int32_
   h_rowptr.assign(h_rp, h_rp + nr + 1);
   h_col.assign(h_c, h_c + nnz);
   std::vector<int32_t> h_diag;
-  if (nr == nc)
+  if (nr <= nc) // square, or owned rows x (owned + ghost) columns
     h_diag.assign(nr, -1);
   for (int32_t r = 0; r < nr; ++r)
     {
@@ -99,7 +99,7 @@ void DevMatrix::create(int32_t nr, int32_t nc, const int32_t *h_rp, const int32_
         {
           S35_REQUIRE(h_c[k] >= 0 && h_c[k] < nc, "matrix: column index out of range");
           S35_REQUIRE(k == h_rp[r] || h_c[k] > h_c[k - 1], "matrix: columns must be strictly ascending within a row");
-          if (nr == nc && h_c[k] == r)
+          if (nr <= nc && h_c[k] == r)
             h_diag[r] = k;
         }
     }
@@ -110,7 +110,7 @@ void DevMatrix::create(int32_t nr, int32_t nc, const int32_t *h_rp, const int32_
     val.upload(h_val, nnz, s);
   else
     val.zero(s);
-  if (nr == nc)
+  if (nr <= nc)
     diag.upload(h_diag, s);
   lanes = pick_lanes(nnz, nr);
   transposed.reset();

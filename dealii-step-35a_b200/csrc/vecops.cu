@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(kBlock) k_add_and_dot(double *result, double *
 
 __global__ void __launch_bounds__(kBlock) k_cg_update(double *result, double *x, double *g, DScal alpha,
                                                        const double *__restrict__ d, const double *__restrict__ h, int64_t n,
-                                                       double *partials, unsigned int *ticket)
+                                                       int post, double *partials, unsigned int *ticket)
 {
   const double av = load_scalar(alpha);
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(kBlock) k_cg_update(double *result, double *x,
       acc += gi * gi;
     }
   acc = block_sum(acc);
-  finish_reduction(acc, partials, ticket, result, kSqrt);
+  finish_reduction(acc, partials, ticket, result, post);
 }
 
 __global__ void __launch_bounds__(kBlock) k_gather_abs_mean(double *result, const double *__restrict__ values,
@@ -291,9 +291,9 @@ void vec_add_and_dot(double *result, double *y, DScal a, const double *x, const 
 }
 
 void vec_cg_update(double *result, double *x, double *g, DScal alpha, const double *d, const double *h, int64_t n,
-                   ReduceWs &ws, cudaStream_t s)
+                   ReducePost post, ReduceWs &ws, cudaStream_t s)
 {
-  S35_LAUNCH(k_cg_update, reduce_grid(n), kBlock, 0, s, result, x, g, alpha, d, h, n, ws.partials.ptr, ws.ticket.ptr);
+  S35_LAUNCH(k_cg_update, reduce_grid(n), kBlock, 0, s, result, x, g, alpha, d, h, n, (int)post, ws.partials.ptr, ws.ticket.ptr);
 }
 
 void vec_gather_abs_mean(double *result, const double *values, const int32_t *idx, int32_t n, ReduceWs &ws, cudaStream_t s)

@@ -57,9 +57,9 @@ void vec_dot(double *result, const double *x, const double *y, int64_t n, Reduce
 // y += a x; *result = y . w (w may alias y)   -- Vector::add_and_dot
 void vec_add_and_dot(double *result, double *y, DScal a, const double *x, const double *w, int64_t n, ReducePost post,
                      ReduceWs &ws, cudaStream_t s);
-// x += alpha d; g += alpha h; *result = sqrt(g . g)   -- the CG update pair (SolverCG)
+// x += alpha d; g += alpha h; *result = g . g (or its square root)   -- the CG update pair (SolverCG)
 void vec_cg_update(double *result, double *x, double *g, DScal alpha, const double *d, const double *h, int64_t n,
-                   ReduceWs &ws, cudaStream_t s);
+                   ReducePost post, ReduceWs &ws, cudaStream_t s);
 // *result = (sum_i |values[idx[i]]|) / n   (mean |diagonal| for ConstraintMatrix::condense)
 void vec_gather_abs_mean(double *result, const double *values, const int32_t *idx, int32_t n, ReduceWs &ws, cudaStream_t s);
 // x += sum_i coef[i] v_i, i < m <= 32 (GMRES solution update); basis vectors are v0 + i * stride

@@ -1,6 +1,7 @@
 // extern "C" layer of include/step35a_host.h
 #include "../../include/step35a_host.h"
 #include "navier_stokes_projection.h"
+#include "partition.h"
 
 #include <chrono>
 #include <cstring>
@@ -21,6 +22,11 @@ struct s35_disc
   std::unique_ptr<s35::Discretization> own_D;       // empty when the handle is a view into a simulation
   std::unique_ptr<Step35::ProblemView> own_view;
   double setup_seconds = 0.0;
+};
+
+struct s35_part
+{
+  std::unique_ptr<s35::LocalProblem> L;
 };
 
 struct s35_sim
@@ -214,6 +220,38 @@ s35_status s35_disc_mesh(const s35_disc *d, const double **vertices, const int32
 }
 
 const int32_t *s35_disc_pres_cell_dofs(const s35_disc *d) { return d && d->D ? d->D->pres.cell_dofs.data() : nullptr; }
+
+s35_status s35_part_create(const s35_disc *d, int32_t n_ranks, int32_t rank, s35_part **out)
+{
+  return guarded([&] {
+    if (!out)
+      throw std::runtime_error("part_create: null argument");
+    *out = nullptr;
+    const s35::Discretization &D = disc_of(d);
+    if (n_ranks < 1 || rank < 0 || rank >= n_ranks)
+      throw std::runtime_error("part_create: bad rank / n_ranks");
+    std::unique_ptr<s35_part> p(new s35_part);
+    p->L = s35::extract_local_problem(D, s35::partition_cells(D.mesh, n_ranks), rank, n_ranks, d->view->problem);
+    *out = p.release();
+  });
+}
+
+void s35_part_destroy(s35_part *p) { delete p; }
+
+const s35_problem *s35_part_problem(const s35_part *p) { return p ? &p->L->problem : nullptr; }
+
+const double *s35_part_initial_pressure(const s35_part *p) { return p ? p->L->initial_pressure.data() : nullptr; }
+
+s35_status s35_disc_partition_cells(const s35_disc *d, int32_t n_ranks, int32_t *cell_rank)
+{
+  return guarded([&] {
+    if (!cell_rank)
+      throw std::runtime_error("partition_cells: null argument");
+    const s35::Discretization &D = disc_of(d);
+    const std::vector<int32_t> r = s35::partition_cells(D.mesh, n_ranks);
+    std::copy(r.begin(), r.end(), cell_rank);
+  });
+}
 
 s35_status s35_mesh_convert(const char *in_file, int32_t dim, const char *out_file)
 {

@@ -183,9 +183,53 @@ typedef struct s35_problem
   double vel_eps, vel_diag_strength;
   int32_t vel_max_iterations, vel_krylov_size, vel_off_diagonals, vel_update_prec;
   int32_t rotational;         /* METHOD_ROTATIONAL = 1, METHOD_STANDARD = 0 */
+
+  /* NULL: the whole problem on one GPU.  Otherwise this is ONE rank's part of a mesh-partitioned problem
+   * (new capability, the reference is single-process): n_vel / n_pres count the rank's local DoFs, owned
+   * ones first, then ghosts grouped by owning rank; every matrix has rows for the owned DoFs only and
+   * columns in local numbering; n_cells counts the cells that touch an owned velocity DoF; constraint lists
+   * hold local indices of owned and ghost DoFs. */
+  const struct s35_dist *dist;
 } s35_problem;
 
+/* ghost-value exchange of one DoF kind: neighbour q receives the owned entries send_idx[send_ptr[q] ..
+ * send_ptr[q+1]) and delivers the ghost entries [n_owned + recv_ptr[q], n_owned + recv_ptr[q+1]) */
+typedef struct s35_halo
+{
+  int32_t n_neighbors;
+  const int32_t *neighbor_rank;
+  const int32_t *send_ptr, *send_idx;
+  const int32_t *recv_ptr;
+} s35_halo;
+
+typedef struct s35_dist
+{
+  int32_t rank, n_ranks;
+  int32_t n_vel_owned, n_pres_owned;
+  int64_t n_vel_global, n_pres_global;
+  s35_halo vel_halo, pres_halo;
+  const int32_t *vel_global_index;  /* [n_vel]  local -> global DoF index */
+  const int32_t *pres_global_index; /* [n_pres] */
+  /* rows of pres_Diff[d]^T for the owned pressure DoFs, columns = local velocity DoFs (owned and ghost): a rank
+   * cannot form them from its own rows of pres_Diff[d], which only cover its owned velocity DoFs */
+  const int32_t *gradT_rowptr, *gradT_col;
+  const double *gradT_val[3];
+} s35_dist;
+
 typedef struct s35_ctx s35_ctx;
+
+/* Joins the calling process (one per GPU) to the communicator the distributed contexts of this process will
+ * use: NCCL over NVLink, `unique_id` = the 128 bytes of an ncclUniqueId created by rank 0 (s35_comm_unique_id)
+ * and handed to the other ranks by the launcher (bench.py broadcasts it with torch.distributed). */
+s35_status s35_comm_unique_id(unsigned char id[128]);
+s35_status s35_comm_init(int32_t rank, int32_t n_ranks, const unsigned char unique_id[128]);
+void s35_comm_finalize(void);
+/* The same partitioned path with the ranks as THREADS of one process that share one GPU (NCCL refuses two
+ * ranks on one device): s35_comm_thread_group(n) once, then every rank's thread calls s35_comm_thread_bind(rank)
+ * before creating its context, and all rank threads make the same sequence of context calls.  For testing the
+ * multi-rank code on a single GPU; not a performance path. */
+s35_status s35_comm_thread_group(int32_t n_ranks);
+s35_status s35_comm_thread_bind(int32_t rank);
 
 /* copies everything it needs to the device; the caller keeps ownership of the host arrays */
 s35_status s35_ctx_create(const s35_problem *problem, s35_ctx **out);

@@ -66,6 +66,19 @@ s35_status s35_disc_mesh(const s35_disc *d, const double **vertices, const int32
 /* pressure cell -> DoF table [n_cells][2^dim] (lexicographic) */
 const int32_t *s35_disc_pres_cell_dofs(const s35_disc *d);
 
+/* ---- one rank's part of the mesh-partitioned problem (multi-GPU path; new capability, the reference is a
+ * single process).  Cells are split by recursive coordinate bisection; a DoF belongs to the lowest rank among
+ * its cells; the local problem holds the owned DoFs and one layer of ghosts. ---- */
+typedef struct s35_part s35_part;
+s35_status s35_part_create(const s35_disc *d, int32_t n_ranks, int32_t rank, s35_part **out);
+void s35_part_destroy(s35_part *p);
+/* the local problem (problem->dist is set); pointers stay valid until s35_part_destroy */
+const s35_problem *s35_part_problem(const s35_part *p);
+/* initial pressure at the local pressure DoFs */
+const double *s35_part_initial_pressure(const s35_part *p);
+/* rank of every cell of the global mesh under the partition into n_ranks parts: [n_cells] */
+s35_status s35_disc_partition_cells(const s35_disc *d, int32_t n_ranks, int32_t *cell_rank);
+
 /* mesh file conversion (tools/pack_meshes.py and the reader round-trip tests) */
 s35_status s35_mesh_convert(const char *in_file, int32_t dim, const char *out_file);
 

@@ -1,0 +1,95 @@
+"""The mesh-partitioned (multi-GPU) code path on ONE GPU: the ranks run as threads of this process and share
+the device (s35_comm_thread_group / s35_comm_thread_bind), so that ghost exchange, cross-rank reductions,
+block-local ILU(0) and the owned/ghost bookkeeping of the time step are exercised without NCCL.  The NCCL
+transport itself is covered by bench.py --gpus N on a multi-GPU box."""
+import threading
+
+import numpy as np
+import pytest
+
+from conftest import rel_diff, start_state
+
+pytestmark = pytest.mark.gpu
+
+
+def run_partitioned(pkg, disc, n_ranks, steps):
+    """returns the global fields gathered from the owners, and per-rank contexts' iteration counts"""
+    pkg.comm_thread_group(n_ranks)
+    out, errors = [None] * n_ranks, []
+
+    def worker(rank):
+        try:
+            pkg.comm_thread_bind(rank)
+            part = pkg.Part(disc, n_ranks, rank)
+            ctx = pkg.Ctx(part.problem)
+            ctx.set_field(pkg.PRES_N, part.initial_pressure)
+            ctx.set_field(pkg.PRES_N_MINUS_1, part.initial_pressure)
+            ctx.advance(2, steps)
+            fields = {"u": [ctx.get_field(pkg.U_N, d) for d in range(disc.dim)], "p": ctx.get_field(pkg.PRES_N),
+                      "phi": ctx.get_field(pkg.PHI_N),
+                      "its": [ctx.solver_stats(d).iterations for d in range(disc.dim)] + [ctx.solver_stats(-1).iterations]}
+            out[rank] = (part, fields)
+            ctx.close()
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=worker, args=(r,), daemon=True) for r in range(n_ranks)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=300)
+    pkg.comm_finalize()
+    assert not errors, errors
+    assert all(o is not None for o in out), "a rank did not finish (dead-locked collective?)"
+    u = [np.full(disc.nv, np.nan) for _ in range(disc.dim)]
+    p, phi = np.full(disc.np_, np.nan), np.full(disc.np_, np.nan)
+    for part, f in out:
+        for d in range(disc.dim):
+            u[d][part.vel_global[:part.nv_owned]] = f["u"][d][:part.nv_owned]
+        p[part.pres_global[:part.np_owned]] = f["p"][:part.np_owned]
+        phi[part.pres_global[:part.np_owned]] = f["phi"][:part.np_owned]
+    # ghost copies agree with their owners
+    for part, f in out:
+        for d in range(disc.dim):
+            assert np.array_equal(f["u"][d], u[d][part.vel_global])
+        assert np.array_equal(f["p"], p[part.pres_global])
+    return u, p, phi, [f["its"] for _, f in out]
+
+
+def run_single(pkg, disc, steps, problem=None):
+    ctx = pkg.Ctx(problem if problem is not None else disc.problem)
+    start_state(pkg, disc, ctx)
+    ctx.advance(2, steps)
+    u = [ctx.get_field(pkg.U_N, d) for d in range(disc.dim)]
+    return u, ctx.get_field(pkg.PRES_N), ctx.get_field(pkg.PHI_N), [ctx.solver_stats(d).iterations for d in range(disc.dim)] + [
+        ctx.solver_stats(-1).iterations]
+
+
+def test_one_rank_partition_reproduces_the_unpartitioned_run_exactly(pkg, make_disc):
+    disc = make_disc("nsbench2.s35m", 2, n_global_refines=1)
+    part = pkg.Part(disc, 1, 0)
+    a = run_single(pkg, disc, 4)
+    b = run_single(pkg, disc, 4, problem=part.problem)
+    for x, y in zip(a[0] + [a[1], a[2]], b[0] + [b[1], b[2]]):
+        assert np.array_equal(x, y)
+    assert a[3] == b[3]
+
+
+@pytest.mark.parametrize("mesh,dim,refines,n_ranks,steps,reynolds",
+                         [("nsbench2.s35m", 2, 1, 2, 5, 100.0), ("nsbench2.s35m", 2, 2, 3, 3, 100.0),
+                          ("cylinder3d.s35m", 3, 0, 2, 2, 20.0), ("cylinder3d.s35m", 3, 0, 4, 2, 20.0)])
+def test_partitioned_time_steps_match_the_single_gpu_run(pkg, make_disc, mesh, dim, refines, n_ranks, steps, reynolds):
+    """The preconditioner changes with the partition (block-local ILU(0)), so the Krylov iterates differ and
+    the fields agree only as far as the solver tolerance determines them: CG stops on the residual, so the
+    pressure is fixed to about eps * cond(pres_Laplace) ~ 1e-11 * 1e4..1e5; the stated tolerance is 1e-6
+    (DESIGN.md section 5), against 1e-8 for identical preconditioners."""
+    disc = make_disc(mesh, dim, n_global_refines=refines, reynolds=reynolds, vel_eps=1e-11)
+    u1, p1, phi1, its1 = run_single(pkg, disc, steps)
+    u, p, phi, its = run_partitioned(pkg, disc, n_ranks, steps)
+    assert all(i == its[0] for i in its)  # every rank takes the same decisions
+    assert its[0][-1] >= its1[-1]         # dropping couplings across the cuts cannot speed CG up
+    scale = max(np.abs(x).max() for x in u1)
+    for d in range(dim):
+        assert np.isfinite(u[d]).all()
+        assert rel_diff(u[d], u1[d], scale) < 1e-6
+    assert rel_diff(p, p1) < 1e-6 and rel_diff(phi, phi1) < 1e-6
