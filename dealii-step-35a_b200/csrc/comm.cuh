@@ -29,6 +29,10 @@ struct Comm
   virtual void allreduce_sum(double *buf, int count, cudaStream_t s) = 0;
   // x[n_owned ..) <- owned values of the neighbours; x[send_idx] -> neighbours
   virtual void exchange(HaloDev &halo, double *x, cudaStream_t s) = 0;
+  // An independent communicator over the same ranks (i = 0, 1, 2), for work that runs concurrently with the
+  // work on this one -- the velocity components, each on its own stream and host thread.  nullptr if the
+  // transport has none; the callers then take turns on the main communicator.
+  virtual Comm *sub(int i) { (void)i; return nullptr; }
 };
 
 // the communicator s35_comm_init created for this process, or nullptr

@@ -205,8 +205,9 @@ Ctx::Ctx(const s35_problem &p)
   prec_pres.create(use_blocks ? plap_blk : plap, s);
   prec_pres.factor(use_blocks ? plap_blk.val : plap.val, diag_strength, s);
   prec_pres.check_pivots(s);
-  // one communicator cannot serve several streams at once: the components take turns on a partition
-  concurrent_components = comm == nullptr;
+  // one communicator cannot serve several streams at once: on a partition the components run concurrently only
+  // if the transport offers a communicator of its own for each of them
+  concurrent_components = comm == nullptr || (comm->sub(0) && comm->sub(1) && comm->sub(2));
   if (const char *t = std::getenv("S35_CONCURRENT_COMPONENTS"))
     concurrent_components = concurrent_components && std::atoi(t) != 0;
   S35_CUDA(cudaEventCreateWithFlags(&fork_event, cudaEventDisableTiming));
@@ -215,7 +216,10 @@ Ctx::Ctx(const s35_problem &p)
       S35_CUDA(cudaStreamCreateWithFlags(&comp_stream[d], cudaStreamNonBlocking));
       S35_CUDA(cudaEventCreateWithFlags(&join_event[d], cudaEventDisableTiming));
       gmres[d].init(nv_own, nv, krylov, concurrent_components ? comp_stream[d] : s);
-      gmres[d].dist = DistLink{comm, use_blocks ? &vel_halo : nullptr};
+      if (use_blocks)
+        comp_halo[d].create(D->vel_halo, nv_own, nv, s);
+      comp_link[d] = DistLink{comm && concurrent_components ? comm->sub(d) : comm, use_blocks ? &comp_halo[d] : nullptr};
+      gmres[d].dist = comp_link[d];
       ws_comp[d].init(concurrent_components ? comp_stream[d] : s);
       S35_CUDA(cudaStreamSynchronize(comp_stream[d]));
     }
@@ -367,8 +371,8 @@ void Ctx::solve_component(int d, bool reinit_prec, cudaStream_t s)
       prec_vel[d].factor(factor_input, diag_strength, s);
       prec_vel[d].check_pivots(s);
     }
-  vec_dot(scal.ptr + 1 + d, force[d], force[d], nv_own, vel_link.local_post(true), ws_comp[d], s);
-  vel_link.finish_sums(scal.ptr + 1 + d, 1, true, s);
+  vec_dot(scal.ptr + 1 + d, force[d], force[d], nv_own, comp_link[d].local_post(true), ws_comp[d], s);
+  comp_link[d].finish_sums(scal.ptr + 1 + d, 1, true, s);
   S35_CUDA(cudaMemcpyAsync(scal_host.ptr + 1 + d, scal.ptr + 1 + d, sizeof(double), cudaMemcpyDeviceToHost, s));
   S35_CUDA(cudaStreamSynchronize(s));
   const double tol = eps * scal_host.ptr[1 + d];
@@ -379,7 +383,7 @@ void Ctx::solve_component(int d, bool reinit_prec, cudaStream_t s)
                                           std::to_string(stats_vel[d].final_residual));
   vec_scatter_set(u_n[d], flow[d].dofs, flow[d].values, flow[d].n_constrained, s); // flow constraints distribute
   vec_scatter_set(u_n[d], wall_dofs, nullptr, n_wall, s);                          // wall constraints distribute
-  vel_link.refresh_ghosts(u_n[d], s);
+  comp_link[d].refresh_ghosts(u_n[d], s);
 }
 
 // step-35a.cc:1268-1338.  The reference runs the dim components as concurrent tasks (Threads::new_task,

@@ -42,6 +42,8 @@ struct Ctx
   Comm *comm = nullptr;
   HaloDev vel_halo, pres_halo;
   DistLink vel_link, pres_link;
+  HaloDev comp_halo[3];           // per velocity component: its own send buffer and communicator
+  DistLink comp_link[3];
   bool use_blocks = false;
   DevMatrix vel_blk, plap_blk;
   DevBuf<int32_t> vel_blk_src, plap_blk_src;
