@@ -39,7 +39,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernels", action="store_true", help="skip the per-kernel roofline pass")
-    ap.add_argument("--deadline", type=int, default=900, help="abort the whole run after this many seconds")
+    ap.add_argument("--deadline", type=int, default=600, help="abort the whole run after this many seconds")
     return ap.parse_args()
 
 

