@@ -30,9 +30,8 @@ print(json.dumps(out))
 
 VARIANT_SETS = {
     "default": [{}],
-    "multi": [{}] + [{"S35_ILU_PER_LANE": str(p)} for p in (1, 2, 4)] + [{"S35_ILU_BLOCKS_PER_SM": str(b)} for b in (1, 2, 8)],
-    "cta": [{}] + [{"S35_ILU_MODE": "cta", "S35_ILU_CTA_G": str(g), "S35_ILU_CTA_P": str(p)}
-                   for g, p in ((8, 2), (8, 4), (16, 2), (16, 4), (32, 2))],
+    "multi": [{}] + [{"S35_ILU_PER_LANE": str(p)} for p in (1, 2, 4)] + [{"S35_ILU_BLOCKS_PER_SM": str(b)} for b in (1, 2, 8)]
+             + [{"S35_ILU_BACKOFF_NS": str(ns)} for ns in (32, 256)] + [{"S35_ILU_ORDER": "natural"}],
 }
 
 
