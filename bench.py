@@ -146,6 +146,15 @@ def cpu_arm(pkg, disc, args, budget_seconds, steps=None, warmup=0):
 
 def main():
     args = parse_args()
+    # stdout carries exactly one JSON line: everything else that lands on file descriptor 1 (the NCCL version
+    # banner, library chatter) is sent to stderr, and the line is written to a private copy of the real stdout
+    real_stdout = os.fdopen(os.dup(1), "w")
+    sys.stdout.flush()
+    os.dup2(2, 1)
+
+    def emit(line):
+        real_stdout.write(json.dumps(line) + "\n")
+        real_stdout.flush()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -186,7 +195,7 @@ def main():
             "e2e": {"value": rate, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "sections_s": sections,
         }
-        print(json.dumps(line))
+        emit(line)
         return 0
 
     import torch
@@ -351,7 +360,7 @@ def main():
             "kernels": kernels, "cpu_baseline": cpu_baseline,
             "setup_s": {"host_discretisation": disc.info.setup_seconds, "device_context": ctx_seconds},
         }
-        print(json.dumps(line))
+        emit(line)
     ctx.close()
     if world > 1:
         pkg.comm_finalize()
