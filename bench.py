@@ -26,6 +26,13 @@ import __graft_entry__ as ge  # noqa: E402
 
 REYNOLDS = {"cylinderextruded": 100.0, "cylinder3d": 20.0, "nsbench2": 100.0}
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch group from the committed `ncu --set full` captures
+# (profiles/prof_*_r01_raw.csv), keyed by (mesh, refines, kernel); other workloads report null
+NCU_TRAFFIC = {
+    ("cylinderextruded", 1, "ilu_apply_pres"): 61.141248e6 + 0.974080e6 + 61.174528e6 + 1.096960e6,  # forward + backward sweep
+    ("cylinderextruded", 1, "spmv_pres"): 58.408448e6 + 0.525312e6,
+}
+
 
 def parse_args():
     ap = argparse.ArgumentParser()
@@ -331,7 +338,9 @@ def main():
         dominant = max(per_step, key=per_step.get)
         k = kernels[dominant]
         roofline = {"kernel": dominant, "bound": "hbm", "achieved": k["GB/s"], "peak": peak, "unit": "GB/s",
-                    "frac": k["frac"], "traffic": None, "peak_source": peak_kind,
+                    "frac": k["frac"], "traffic": NCU_TRAFFIC.get((args.mesh, args.refines, dominant)) if world == 1 else None,
+                    "algorithmic_bytes": k["algorithmic_bytes"], "ms": k["ms"], "launches": k["launches"],
+                    "peak_source": peak_kind,
                     "share_of_step": per_step[dominant] / (1e3 * elapsed / args.steps),
                     "note": "critical-path bound (dependency levels x L2 latency), not bandwidth bound: see DESIGN.md"
                     if dominant.startswith("ilu") else ""}
