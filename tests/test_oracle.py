@@ -275,3 +275,28 @@ def test_oracle_reports_no_convergence(pkg, ob, make_disc):
     start_state(pkg, disc, orc)
     with pytest.raises(ob.OracleError):
         orc.advance(2, 1)
+
+
+def test_config_1_hundred_steps_drag_and_lift(pkg, ob, make_disc):
+    """BASELINE.json config 1 (nsbench2.inp, Re = 100, 100 time steps): both CPU restatements agree on the
+    fields to 1e-8 and on the drag / lift coefficients to 1e-6 over the whole run."""
+    import oracle_np
+    disc = make_disc("nsbench2.s35m", 2, final_time=0.0505)
+    orc = ob.Oracle(disc.problem)
+    start_state(pkg, disc, orc)
+    v, c, b, ids = disc.mesh()
+    ref = oracle_np.NumpyStep35(2, v, c, b, ids, dt=5e-4, reynolds=100.0, eps=1e-8, vel_numbering=disc.vel_support,
+                                pres_numbering=disc.pres_support)
+    n_steps = int((0.0505 - 0.0) / 5e-4) - 1  # run() does steps n = 2 .. (T - t0)/dt (step-35a.cc:1174,1190-1191)
+    assert n_steps == 100
+    for first in range(2, 2 + n_steps, 25):
+        orc.advance(first, 25)
+        ref.advance(first, 25)
+        u_o = np.concatenate([orc.get_field(pkg.U_N, d) for d in range(2)])
+        u_r = np.concatenate(ref.u_n)
+        assert rel_diff(u_o, u_r) < 1e-8 and rel_diff(orc.get_field(pkg.PRES_N), ref.pres_n) < 1e-8
+        cd_o = disc.drag_lift(100.0, u_o, orc.get_field(pkg.PRES_N))
+        cd_r = disc.drag_lift(100.0, u_r, ref.pres_n)
+        assert np.abs(cd_o - cd_r).max() <= 1e-6 * max(1.0, np.abs(cd_r).max())
+    # after the impulsive start has decayed the drag on the square obstacle is positive and O(1)
+    assert 0.5 < cd_o[0] < 50 and abs(cd_o[1]) < 5
