@@ -437,6 +437,7 @@ s35_status s35_ctx_get_operator_values(s35_ctx *ctx, s35_operator op, int32_t co
   return guarded([&] {                                   \
     S35_REQUIRE(ctx != nullptr, "null context");         \
     Ctx &c = *ctx->c;                                    \
+    S35_CUDA(cudaSetDevice(c.device));                   \
     expr;                                                \
     c.resolve_sections();                                \
   })
