@@ -1,59 +1,63 @@
-// The step-35a program (reference main(), step-35a.cc:1712-1760): reads
-// "parameter-file.prm" from the current directory, builds the solver and runs it.
-// The reference fixes dimension and mesh at compile time (step-35a.cc:748,1726);
-// here they can be given on the command line:  step-35a [dim [mesh-file [prm-file]]]
+// The step-35a program: same contract as the reference's main() (step-35a.cc:1712-1760) -- read
+// "parameter-file.prm" from the current directory, build the solver, run it, return 1 with a banner on stderr if
+// anything throws.  The reference fixes dimension and mesh at compile time (step-35a.cc:748,1726); here they are
+// optional command-line arguments:
+//
+//     step-35a [dim [mesh-file [parameter-file]]]
 #include "navier_stokes_projection.h"
 
 #include <cstdlib>
 #include <iostream>
+#include <string>
+
+namespace {
+
+const char *const kRule = "----------------------------------------------------";
+
+int report_failure(const char *what)
+{
+  std::cerr << "\n\n" << kRule << "\n";
+  if (what)
+    std::cerr << "Exception on processing: \n" << what << "\n";
+  else
+    std::cerr << "Unknown exception!\n";
+  std::cerr << "Aborting!\n" << kRule << std::endl;
+  return 1;
+}
+
+template <int dim>
+void solve(const Step35::RunTimeParameters::Data_Storage &data, const std::string &mesh)
+{
+  Step35::NavierStokesProjection<dim> problem(data, mesh);
+  problem.run(data.verbose, data.output_interval);
+}
+
+} // namespace
 
 int main(int argc, char **argv)
 {
+  const int dim = argc > 1 ? std::atoi(argv[1]) : 3;
+  const std::string mesh = argc > 2 ? argv[2] : "";
+  const std::string prm = argc > 3 ? argv[3] : "parameter-file.prm";
   try
     {
-      using namespace Step35;
-      const int dim = argc > 1 ? std::atoi(argv[1]) : 3;
-      const std::string mesh = argc > 2 ? argv[2] : "";
-      const std::string prm = argc > 3 ? argv[3] : "parameter-file.prm";
-      RunTimeParameters::Data_Storage data;
+      Step35::RunTimeParameters::Data_Storage data;
       data.read_data(prm.c_str());
-      if (dim == 2)
+      switch (dim)
         {
-          NavierStokesProjection<2> test(data, mesh);
-          test.run(data.verbose, data.output_interval);
+        case 2: solve<2>(data, mesh); break;
+        case 3: solve<3>(data, mesh); break;
+        default: throw std::runtime_error("the first argument (dimension) must be 2 or 3");
         }
-      else if (dim == 3)
-        {
-          NavierStokesProjection<3> test(data, mesh);
-          test.run(data.verbose, data.output_interval);
-        }
-      else
-        throw std::runtime_error("dim must be 2 or 3");
     }
-  catch (std::exception &exc)
+  catch (const std::exception &e)
     {
-      std::cerr << std::endl
-                << std::endl
-                << "----------------------------------------------------" << std::endl;
-      std::cerr << "Exception on processing: " << std::endl
-                << exc.what() << std::endl
-                << "Aborting!" << std::endl
-                << "----------------------------------------------------" << std::endl;
-      return 1;
+      return report_failure(e.what());
     }
   catch (...)
     {
-      std::cerr << std::endl
-                << std::endl
-                << "----------------------------------------------------" << std::endl;
-      std::cerr << "Unknown exception!" << std::endl
-                << "Aborting!" << std::endl
-                << "----------------------------------------------------" << std::endl;
-      return 1;
+      return report_failure(nullptr);
     }
-  std::cout << "----------------------------------------------------" << std::endl
-            << "Apparently everything went fine!" << std::endl
-            << "Don't forget to brush your teeth :-)" << std::endl
-            << std::endl;
+  std::cout << kRule << "\nThe run finished without errors.\n" << std::endl;
   return 0;
 }
