@@ -193,61 +193,79 @@ void NavierStokesProjection<dim>::save_checkpoint()
   H5::save(file, "pres_n_minus_1", p);
 }
 
+namespace {
+
+// Which step numbers run() visits.  Fresh start: n = 2 .. (T - t0)/dt, and the advection matrix is assembled
+// once before step 2.  Restart from a checkpoint: n = t0/dt .. t0/dt + (T - t0)/dt, and -- a quirk of the
+// reference kept here -- the matrix is NOT assembled before the first diffusion step, because the prologue is
+// tied to n == 0 (step-35a.cc:1174-1191, 1204-1208).
+struct StepRange
+{
+  unsigned int first, last, prologue_at;
+};
+
+StepRange step_range(double t_0, double T, double dt, bool restart)
+{
+  const unsigned int n_steps = static_cast<unsigned int>((T - t_0) / dt);
+  if (!restart)
+    return StepRange{2u, n_steps, 2u};
+  const unsigned int first = static_cast<unsigned int>(t_0 / dt);
+  return StepRange{first, first + n_steps, 0u};
+}
+
+} // namespace
+
 template <int dim>
 unsigned int NavierStokesProjection<dim>::n_time_steps() const
 {
-  // step-35a.cc:1174,1190-1191: n runs from 2 to n_steps on a fresh start
-  const unsigned int n_steps = static_cast<unsigned int>((T - t_0) / dt);
-  return load_checkpoint_file_name.empty() ? (n_steps >= 1 ? n_steps - 1 : 0) : n_steps + 1;
+  const StepRange r = step_range(t_0, T, dt, !load_checkpoint_file_name.empty());
+  return r.last >= r.first ? r.last - r.first + 1 : 0;
 }
 
 template <int dim>
 void NavierStokesProjection<dim>::run(const bool verbose, const unsigned int output_interval)
 {
-  auto verbose_cout = [&](const char *msg) {
+  auto say = [&](const char *msg) {
     if (verbose)
       std::cout << msg << std::endl;
   };
-  const unsigned int n_steps = static_cast<unsigned int>((T - t_0) / dt);
-  unsigned int step_start_n = 2;
-  unsigned int step_start_offset_n = 2;
-  if (load_checkpoint_file_name.size() == 0)
-    output_results(1, t_0);
+  const bool restart = !load_checkpoint_file_name.empty();
+  const StepRange steps = step_range(t_0, T, dt, restart);
+  if (restart)
+    load_checkpoint();
   else
+    output_results(1, t_0);
+
+  for (unsigned int n = steps.first; n <= steps.last; ++n)
     {
-      load_checkpoint();
-      step_start_n = static_cast<unsigned int>(t_0 / dt);
-      step_start_offset_n = 0;
-    }
-  for (unsigned int n = step_start_n; n <= step_start_n + n_steps - step_start_offset_n; ++n)
-    {
-      const double current_time = (t_0 + (n - step_start_n + step_start_offset_n) * dt);
+      const double current_time = t_0 + (n - steps.first + steps.prologue_at) * dt;
       if (n % output_interval == 0)
         {
-          verbose_cout("Plotting Solution");
+          say("Plotting Solution");
           output_results(n, current_time);
         }
       std::cout << "Step = " << n << " Time = " << current_time << std::endl;
-      verbose_cout("  Interpolating the velocity ");
-      // both of these are needed to do the diffusion step
-      if (n == step_start_offset_n)
+      say("  Interpolating the velocity ");
+      if (n == steps.prologue_at)
         {
           interpolate_velocity();
           assemble_advection_term();
         }
-      verbose_cout("  Diffusion Step");
-      if (n % vel_update_prec == 0)
-        verbose_cout("    With reinitialization of the preconditioner");
-      diffusion_step((n % vel_update_prec == 0) || (n == step_start_n));
+      say("  Diffusion Step");
+      const bool refresh_preconditioner = (n % vel_update_prec == 0);
+      if (refresh_preconditioner)
+        say("    With reinitialization of the preconditioner");
+      diffusion_step(refresh_preconditioner || n == steps.first);
       interpolate_velocity();
-      // the reference runs these two as concurrent tasks (step-35a.cc:1219-1235)
+      // two concurrent tasks in the reference (step-35a.cc:1219-1235); they touch disjoint data
       assemble_advection_term();
-      verbose_cout("  Projection Step");
+      say("  Projection Step");
       projection_step();
-      verbose_cout("  Updating the Pressure");
+      say("  Updating the Pressure");
       update_pressure();
       if (verbose)
         {
+          // stands in for deal.II's deallog output of the solvers (step-35a.cc:1724)
           s35_solver_stats st;
           for (int d = 0; d < dim; ++d)
             {
