@@ -144,53 +144,60 @@ void NavierStokesProjection<dim>::initialize()
     }
 }
 
+// The checkpoint set of the reference (step-35a.cc:856-900): dataset name -> state vector.
+struct CheckpointEntry
+{
+  std::string dataset;
+  s35_field field;
+  int component;
+};
+
+static std::vector<CheckpointEntry> checkpoint_entries(int dim)
+{
+  std::vector<CheckpointEntry> e;
+  for (int d = 0; d < dim; ++d)
+    {
+      e.push_back({"u_n" + std::to_string(d), S35_U_N, d});
+      e.push_back({"u_n_minus_1" + std::to_string(d), S35_U_N_MINUS_1, d});
+    }
+  e.push_back({"phi_n", S35_PHI_N, 0});
+  e.push_back({"phi_n_minus_1", S35_PHI_N_MINUS_1, 0});
+  e.push_back({"pres_n", S35_PRES_N, 0});
+  e.push_back({"pres_n_minus_1", S35_PRES_N_MINUS_1, 0});
+  return e;
+}
+
 template <int dim>
 void NavierStokesProjection<dim>::load_checkpoint()
 {
-  if (load_checkpoint_file_name.size() == 0)
+  if (load_checkpoint_file_name.empty())
     return;
-  std::vector<double> v;
-  for (int block_n = 0; block_n < dim; ++block_n)
+  std::vector<double> values;
+  for (const CheckpointEntry &e : checkpoint_entries(dim))
     {
-      H5::load(load_checkpoint_file_name, "u_n" + std::to_string(block_n), v);
-      check(s35_ctx_set_field(ctx, S35_U_N, block_n, v.data()));
-      H5::load(load_checkpoint_file_name, "u_n_minus_1" + std::to_string(block_n), v);
-      check(s35_ctx_set_field(ctx, S35_U_N_MINUS_1, block_n, v.data()));
+      H5::load(load_checkpoint_file_name, e.dataset, values);
+      const size_t expected = (e.field == S35_U_N || e.field == S35_U_N_MINUS_1) ? disc->vel.n_dofs : disc->pres.n_dofs;
+      if (values.size() != expected)
+        throw std::runtime_error("checkpoint dataset " + e.dataset + " has the wrong length");
+      check(s35_ctx_set_field(ctx, e.field, e.component, values.data()));
     }
-  H5::load(load_checkpoint_file_name, "phi_n", v);
-  check(s35_ctx_set_field(ctx, S35_PHI_N, 0, v.data()));
-  H5::load(load_checkpoint_file_name, "phi_n_minus_1", v);
-  check(s35_ctx_set_field(ctx, S35_PHI_N_MINUS_1, 0, v.data()));
-  H5::load(load_checkpoint_file_name, "pres_n", v);
-  check(s35_ctx_set_field(ctx, S35_PRES_N, 0, v.data()));
-  H5::load(load_checkpoint_file_name, "pres_n_minus_1", v);
-  check(s35_ctx_set_field(ctx, S35_PRES_N_MINUS_1, 0, v.data()));
 }
 
 template <int dim>
 void NavierStokesProjection<dim>::save_checkpoint()
 {
-  if (save_checkpoint_file_name.size() == 0)
+  if (save_checkpoint_file_name.empty())
     return;
   const std::string file = output_directory + "/" + save_checkpoint_file_name;
   std::cout << "outfile name is '" << save_checkpoint_file_name << "'" << std::endl;
   std::remove(file.c_str());
-  std::vector<double> v(disc->vel.n_dofs), p(disc->pres.n_dofs);
-  for (int block_n = 0; block_n < dim; ++block_n)
+  std::vector<double> values;
+  for (const CheckpointEntry &e : checkpoint_entries(dim))
     {
-      check(s35_ctx_get_field(ctx, S35_U_N, block_n, v.data()));
-      H5::save(file, "u_n" + std::to_string(block_n), v);
-      check(s35_ctx_get_field(ctx, S35_U_N_MINUS_1, block_n, v.data()));
-      H5::save(file, "u_n_minus_1" + std::to_string(block_n), v);
+      values.resize((e.field == S35_U_N || e.field == S35_U_N_MINUS_1) ? disc->vel.n_dofs : disc->pres.n_dofs);
+      check(s35_ctx_get_field(ctx, e.field, e.component, values.data()));
+      H5::save(file, e.dataset, values);
     }
-  check(s35_ctx_get_field(ctx, S35_PHI_N, 0, p.data()));
-  H5::save(file, "phi_n", p);
-  check(s35_ctx_get_field(ctx, S35_PHI_N_MINUS_1, 0, p.data()));
-  H5::save(file, "phi_n_minus_1", p);
-  check(s35_ctx_get_field(ctx, S35_PRES_N, 0, p.data()));
-  H5::save(file, "pres_n", p);
-  check(s35_ctx_get_field(ctx, S35_PRES_N_MINUS_1, 0, p.data()));
-  H5::save(file, "pres_n_minus_1", p);
 }
 
 namespace {
