@@ -46,6 +46,8 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernels", action="store_true", help="skip the per-kernel roofline pass")
+    ap.add_argument("--ilu-blocks", type=int, default=1,
+                    help="GATED ALTERNATIVE (not the reference's preconditioner): ILU(0) of k index-range blocks")
     ap.add_argument("--deadline", type=int, default=600, help="abort the whole run after this many seconds")
     return ap.parse_args()
 
@@ -234,6 +236,8 @@ def main():
         pkg.comm_init(rank, world, bytes(uid.cpu().tolist()))
         part = pkg.Part(disc, world, rank)
     problem = part.problem if part else disc.problem
+    if args.ilu_blocks > 1:
+        problem = pkg.with_ilu_blocks(problem, args.ilu_blocks)
     initial_pressure = part.initial_pressure if part else disc.initial_pressure
     nv, np_ = (part.nv, part.np_) if part else (disc.nv, disc.np_)
     t0 = time.perf_counter()
@@ -360,6 +364,8 @@ def main():
             "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(args), "dof": dof, "n_vel_per_component": disc.nv, "n_pres": disc.np_,
                        "cells": disc.n_cells,
+                       "preconditioner": "ILU(0) as the reference's SparseILU" if args.ilu_blocks <= 1 else
+                                         "GATED ALTERNATIVE: ILU(0) of %d index-range blocks" % args.ilu_blocks,
                        "parallelism": ("mesh partition x%d (coordinate bisection, NCCL ghost exchange + all-reduce, "
                                        "block-local ILU(0))" % world) if world > 1 else "single GPU",
                        "l2": "working set (%.0f MB of matrices) exceeds L2; kernel benchmarks flush L2 between launches"

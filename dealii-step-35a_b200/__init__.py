@@ -69,7 +69,7 @@ class Problem(C.Structure):
         ("n_proj", C.c_int32), ("proj_dofs", c_int32_p),
         ("dt", C.c_double), ("reynolds", C.c_double), ("vel_eps", C.c_double), ("vel_diag_strength", C.c_double),
         ("vel_max_iterations", C.c_int32), ("vel_krylov_size", C.c_int32), ("vel_off_diagonals", C.c_int32),
-        ("vel_update_prec", C.c_int32), ("rotational", C.c_int32),
+        ("vel_update_prec", C.c_int32), ("rotational", C.c_int32), ("ilu_blocks", C.c_int32),
         ("dist", C.POINTER(Dist)),
     ]
 
@@ -414,6 +414,15 @@ def comm_thread_group(n_ranks):
 
 def comm_thread_bind(rank):
     check(lib().s35_comm_thread_bind(rank))
+
+
+def with_ilu_blocks(problem, k):
+    """Copy of a problem description with the gated block-ILU alternative switched on (s35_problem.ilu_blocks)."""
+    src = problem.contents if hasattr(problem, "contents") else problem
+    p = Problem.from_buffer_copy(src)
+    p.ilu_blocks = int(k)
+    p._keepalive = problem
+    return p
 
 
 class Ctx:

@@ -175,21 +175,30 @@ Ctx::Ctx(const s35_problem &p)
   // preconditioners (pressure: built once, step-35a.cc:1070-1074) and solvers
   // On a partition the preconditioner is the ILU(0) of the rank's diagonal block (owned rows x owned columns):
   // couplings to ghost columns are dropped.  Ghost columns sort last, so the block is a prefix of every row.
+  // The gated alternative ilu_blocks = k cuts the owned rows into k contiguous ranges and keeps only the
+  // couplings inside a range (see the header); k = 1 keeps everything.
+  ilu_blocks = std::max<int32_t>(1, p.ilu_blocks);
+  if (const char *t = std::getenv("S35_ILU_BLOCKS"))
+    ilu_blocks = std::max(1, std::atoi(t));
   auto make_block = [&](const DevMatrix &A, int32_t n_own, DevMatrix &blk, DevBuf<int32_t> &src) {
+    auto range_of = [&](int32_t i) { return (int32_t)((int64_t)i * ilu_blocks / n_own); };
     std::vector<int32_t> rp(n_own + 1, 0), cl, from;
     for (int32_t r = 0; r < n_own; ++r)
       {
+        const int32_t br = range_of(r);
         for (int32_t k = A.h_rowptr[r]; k < A.h_rowptr[r + 1] && A.h_col[k] < n_own; ++k)
-          {
-            cl.push_back(A.h_col[k]);
-            from.push_back(k);
-          }
+          if (ilu_blocks == 1 || range_of(A.h_col[k]) == br)
+            {
+              cl.push_back(A.h_col[k]);
+              from.push_back(k);
+            }
         rp[r + 1] = (int32_t)cl.size();
       }
     blk.create(n_own, n_own, rp.data(), cl.data(), nullptr, s);
     src.upload(from, s);
   };
-  use_blocks = D != nullptr && (nv_own < nv || np_own < np);
+  const bool use_halo = D != nullptr && (nv_own < nv || np_own < np);
+  use_blocks = use_halo || ilu_blocks > 1;
   if (use_blocks)
     {
       make_block(vel_adv, nv_own, vel_blk, vel_blk_src);
@@ -197,6 +206,9 @@ Ctx::Ctx(const s35_problem &p)
       for (int d = 0; d < dim; ++d)
         blk_val[d].alloc(vel_blk.nnz);
       gather_values(plap_blk.val, plap.val, plap_blk_src, plap_blk.nnz, s);
+    }
+  if (use_halo)
+    {
       vel_halo.create(D->vel_halo, nv_own, nv, s);
       pres_halo.create(D->pres_halo, np_own, np, s);
     }
@@ -216,16 +228,16 @@ Ctx::Ctx(const s35_problem &p)
       S35_CUDA(cudaStreamCreateWithFlags(&comp_stream[d], cudaStreamNonBlocking));
       S35_CUDA(cudaEventCreateWithFlags(&join_event[d], cudaEventDisableTiming));
       gmres[d].init(nv_own, nv, krylov, concurrent_components ? comp_stream[d] : s);
-      if (use_blocks)
+      if (use_halo)
         comp_halo[d].create(D->vel_halo, nv_own, nv, s);
-      comp_link[d] = DistLink{comm && concurrent_components ? comm->sub(d) : comm, use_blocks ? &comp_halo[d] : nullptr};
+      comp_link[d] = DistLink{comm && concurrent_components ? comm->sub(d) : comm, use_halo ? &comp_halo[d] : nullptr};
       gmres[d].dist = comp_link[d];
       ws_comp[d].init(concurrent_components ? comp_stream[d] : s);
       S35_CUDA(cudaStreamSynchronize(comp_stream[d]));
     }
   cg.init(np_own, np, s);
-  cg.dist = DistLink{comm, use_blocks ? &pres_halo : nullptr};
-  vel_link = DistLink{comm, use_blocks ? &vel_halo : nullptr};
+  cg.dist = DistLink{comm, use_halo ? &pres_halo : nullptr};
+  vel_link = DistLink{comm, use_halo ? &vel_halo : nullptr};
   pres_link = cg.dist;
   ws.init(s);
   scal.alloc(8);

@@ -44,7 +44,8 @@ struct Ctx
   DistLink vel_link, pres_link;
   HaloDev comp_halo[3];           // per velocity component: its own send buffer and communicator
   DistLink comp_link[3];
-  bool use_blocks = false;
+  bool use_blocks = false;        // the ILU(0) factors live on a filtered pattern (partition and / or ilu_blocks)
+  int32_t ilu_blocks = 1;
   DevMatrix vel_blk, plap_blk;
   DevBuf<int32_t> vel_blk_src, plap_blk_src;
   DevBuf<double> blk_val[3];

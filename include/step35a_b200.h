@@ -184,6 +184,14 @@ typedef struct s35_problem
   int32_t vel_max_iterations, vel_krylov_size, vel_off_diagonals, vel_update_prec;
   int32_t rotational;         /* METHOD_ROTATIONAL = 1, METHOD_STANDARD = 0 */
 
+  /* GATED ALTERNATIVE, not the reference's preconditioner.  0 or 1: ILU(0) of the whole matrix, exactly what
+   * SparseILU computes (the default).  k > 1: the rows are cut into k contiguous index ranges (slabs of the
+   * Cuthill-McKee numbering) and couplings between different ranges are dropped from the FACTORS only; the
+   * matrices are untouched.  The k blocks are independent, so the dependency chains of the substitutions get
+   * about k times shorter and k times wider -- the single-GPU analogue of what the mesh partition does across
+   * GPUs.  Iteration counts rise; fields agree with the default to the solver tolerance. */
+  int32_t ilu_blocks;
+
   /* NULL: the whole problem on one GPU.  Otherwise this is ONE rank's part of a mesh-partitioned problem
    * (new capability, the reference is single-process): n_vel / n_pres count the rank's local DoFs, owned
    * ones first, then ghosts grouped by owning rank; every matrix has rows for the owned DoFs only and

@@ -199,3 +199,23 @@ def test_device_path_reproduces_the_golden_vectors(pkg, make_disc, name):
     assert [ctx.solver_stats(d).iterations for d in range(dim)] == list(g["its_vel"])
     assert abs(ctx.solver_stats(-1).iterations - int(g["its_proj"])) <= 1
     check_against_golden(pkg, disc, ctx, g, GOLDEN_TOL[name])
+
+
+def test_block_ilu_gated_alternative_reaches_the_same_fields(pkg, make_disc):
+    """s35_problem.ilu_blocks > 1 swaps the preconditioner (documented as a gated alternative): the iteration counts
+    move, the fields agree with the default to the solver tolerance (eps = 1e-12 here; tolerance 5e-6 as for the
+    partitioned runs, same conditioning argument)."""
+    disc = make_disc("nsbench2.s35m", 2, n_global_refines=2, vel_eps=1e-12)
+    fields = []
+    its = []
+    for k in (1, 6):
+        ctx = pkg.Ctx(pkg.with_ilu_blocks(disc.problem, k))
+        ctx.set_field(pkg.PRES_N, disc.initial_pressure)
+        ctx.set_field(pkg.PRES_N_MINUS_1, disc.initial_pressure)
+        ctx.advance(2, 3)
+        fields.append([ctx.get_field(pkg.U_N, d) for d in range(2)] + [ctx.get_field(pkg.PRES_N)])
+        its.append(ctx.solver_stats(-1).iterations)
+        ctx.close()
+    for a, b in zip(*fields):
+        assert np.max(np.abs(a - b)) <= 5e-6 * max(1.0, np.max(np.abs(a)))
+    assert its[1] >= its[0]          # a weaker preconditioner cannot need fewer CG iterations here
