@@ -91,11 +91,19 @@ double add_and_dot(double *self, double a, const double *V, const double *W, int
   return s;
 }
 
-// SparseILU<double>::initialize [A.3]: IKJ ILU(0) in place, inverse pivot on the diagonal
-void ilu0_factor(const Csr &P, const double *a, double strengthen, double *lu)
+// SparseILU<double>::initialize [A.3]: IKJ ILU(0) in place, inverse pivot on the diagonal.
+// blocks > 1 is the gated alternative of s35_problem.ilu_blocks (no counterpart in the reference): couplings
+// between different index ranges are zeroed before factoring.  They stay exactly zero through the elimination
+// and add exact zeros in the substitutions, so this equals ILU(0) of the block-diagonal part entry for entry.
+void ilu0_factor(const Csr &P, const double *a, double strengthen, double *lu, int blocks = 1)
 {
   const int n = P.n_rows;
   std::copy(a, a + P.nnz(), lu);
+  if (blocks > 1)
+    for (int r = 0; r < n; ++r)
+      for (int k = P.rowptr[r]; k < P.rowptr[r + 1]; ++k)
+        if ((long long)P.col[k] * blocks / n != (long long)r * blocks / n)
+          lu[k] = 0.0;
   if (strengthen > 0.0)
     for (int r = 0; r < n; ++r)
       {
@@ -471,6 +479,7 @@ struct oracle_ctx
 {
   int dim = 0, n_cells = 0, nv = 0, np = 0;
   double dt = 0, Re = 0, eps = 0, diag_strength = 0;
+  int ilu_blocks = 1;
   int max_its = 0, krylov = 0, update_prec = 0;
   bool rotational = true;
   FE *fe = nullptr;
@@ -760,6 +769,7 @@ int oracle_create(const s35_problem *p, oracle_ctx **out)
     c->Re = p->reynolds;
     c->eps = p->vel_eps;
     c->diag_strength = p->vel_diag_strength;
+    c->ilu_blocks = std::max(1, (int)p->ilu_blocks);
     c->max_its = p->vel_max_iterations;
     c->krylov = p->vel_krylov_size;
     c->update_prec = p->vel_update_prec;
@@ -799,7 +809,7 @@ int oracle_create(const s35_problem *p, oracle_ctx **out)
       v->assign(c->np, 0.);
     // pressure preconditioners are built once (ref:1070-1075)
     c->prec_pres.resize(c->plap.nnz());
-    ilu0_factor(c->plap, c->pres_laplace.data(), c->diag_strength, c->prec_pres.data());
+    ilu0_factor(c->plap, c->pres_laplace.data(), c->diag_strength, c->prec_pres.data(), c->ilu_blocks);
     build_mass_cholesky(*c);
     std::memset(c->stats_vel, 0, sizeof(c->stats_vel));
     c->stats_proj = c->stats_mass = s35_solver_stats{0, 0., 0., 0.};
@@ -919,7 +929,7 @@ int oracle_diffusion_step(oracle_ctx *c, int reinit_prec)
             {
               condense(c->velc, c->vel_it[d].data(), c->force[d].data(), c->flow_dofs[d], c->flow_vals[d]);
               if (reinit_prec)
-                ilu0_factor(c->velc, c->vel_it[d].data(), c->diag_strength, c->prec_vel[d].data());
+                ilu0_factor(c->velc, c->vel_it[d].data(), c->diag_strength, c->prec_vel[d].data(), c->ilu_blocks);
               // diffusion_component_solve (ref:1330-1338)
               const double tol = c->eps * l2_norm(c->force[d].data(), nv);
               const bool ok = gmres(c->velc, c->vel_it[d].data(), c->prec_vel[d].data(), c->u_n[d].data(), c->force[d].data(),

@@ -219,3 +219,23 @@ def test_block_ilu_gated_alternative_reaches_the_same_fields(pkg, make_disc):
     for a, b in zip(*fields):
         assert np.max(np.abs(a - b)) <= 5e-6 * max(1.0, np.max(np.abs(a)))
     assert its[1] >= its[0]          # a weaker preconditioner cannot need fewer CG iterations here
+
+
+def test_block_ilu_gated_alternative_against_the_oracle(pkg, ob, make_disc):
+    """The oracle restates the gated alternative too (couplings between index ranges zeroed before ILU(0)), so the
+    device path is checked against it like the default: same iteration counts, fields to 1e-8."""
+    disc = make_disc("nsbench2.s35m", 2)
+    problem = pkg.with_ilu_blocks(disc.problem, 5)
+    ctx, orc = pkg.Ctx(problem), ob.Oracle(problem)
+    start_state(pkg, disc, ctx, orc)
+    ctx.advance(2, 4)
+    orc.advance(2, 4)
+    for comp in (0, 1, -1):
+        assert ctx.solver_stats(comp).iterations == orc.solver_stats(comp).iterations
+    for d in range(2):
+        assert rel_diff(ctx.get_field(pkg.U_N, d), orc.get_field(pkg.U_N, d)) < 1e-8
+    assert rel_diff(ctx.get_field(pkg.PRES_N), orc.get_field(pkg.PRES_N)) < 1e-8
+    exact = ob.Oracle(disc.problem)
+    start_state(pkg, disc, exact)
+    exact.advance(2, 4)
+    assert not np.array_equal(exact.get_field(pkg.PRES_N), orc.get_field(pkg.PRES_N))   # the option changes the solve

@@ -300,3 +300,21 @@ def test_config_1_hundred_steps_drag_and_lift(pkg, ob, make_disc):
         assert np.abs(cd_o - cd_r).max() <= 1e-6 * max(1.0, np.abs(cd_r).max())
     # after the impulsive start has decayed the drag on the square obstacle is positive and O(1)
     assert 0.5 < cd_o[0] < 50 and abs(cd_o[1]) < 5
+
+
+def test_block_ilu_alternative_in_the_oracle(pkg, ob, make_disc):
+    """s35_problem.ilu_blocks (gated alternative, no counterpart in the reference): another preconditioner, the same
+    converged fields to the solver tolerance, no fewer CG iterations."""
+    disc = make_disc("nsbench2.s35m", 2, n_global_refines=1, vel_eps=1e-12)
+    runs = []
+    for k in (1, 4):
+        orc = ob.Oracle(pkg.with_ilu_blocks(disc.problem, k))
+        start_state(pkg, disc, orc)
+        orc.advance(2, 3)
+        runs.append(([orc.get_field(pkg.U_N, d) for d in range(2)] + [orc.get_field(pkg.PRES_N)],
+                     orc.solver_stats(-1).iterations))
+        orc.close()
+    for a, b in zip(runs[0][0], runs[1][0]):
+        assert not np.array_equal(a, b)
+        assert np.max(np.abs(a - b)) <= 5e-6 * max(1.0, np.max(np.abs(a)))
+    assert runs[1][1] >= runs[0][1]
