@@ -55,6 +55,11 @@ s35_status guarded(F &&f)
       g_last_error = e.what();
       return S35_ERR_INVALID;
     }
+  catch (...)
+    {
+      g_last_error = "unknown failure";   // nothing may unwind through the C boundary
+      return S35_ERR_INVALID;
+    }
 }
 
 void require_device()

@@ -46,6 +46,19 @@ std::vector<int32_t> color_cells_by_dofs(int32_t n_cells, int dpc, int32_t n_dof
 
 Ctx::Ctx(const s35_problem &p)
 {
+  try
+    {
+      build(p);
+    }
+  catch (...)
+    {
+      release_handles();   // a constructor that throws gets no destructor call
+      throw;
+    }
+}
+
+void Ctx::build(const s35_problem &p)
+{
   S35_REQUIRE(p.dim == 2 || p.dim == 3, "problem: dim must be 2 or 3");
   S35_REQUIRE(p.n_cells > 0 && p.n_vel > 0 && p.n_pres > 0, "problem: empty mesh");
   S35_REQUIRE(p.cell_vertices && p.vel_cell_dofs, "problem: null geometry arrays");
@@ -53,6 +66,11 @@ Ctx::Ctx(const s35_problem &p)
   S35_REQUIRE(p.grad_rowptr && p.grad_col && p.plap_rowptr && p.plap_col && p.plap_val && p.pmass_rowptr && p.pmass_col &&
                 p.pmass_val,
               "problem: null pressure matrices");
+  S35_REQUIRE(p.n_wall >= 0 && p.n_proj >= 0 && (p.n_wall == 0 || p.wall_dofs) && (p.n_proj == 0 || p.proj_dofs),
+              "problem: null or negative-length constraint lists");
+  for (int d = 0; d < p.dim; ++d)
+    S35_REQUIRE(p.n_flow[d] >= 0 && (p.n_flow[d] == 0 || (p.flow_dofs[d] && p.flow_vals[d])),
+                "problem: null or negative-length inflow constraint lists");
   S35_REQUIRE(p.dt > 0 && p.reynolds > 0, "problem: dt and Reynolds must be positive");
   S35_REQUIRE(p.vel_max_iterations >= 1 && p.vel_update_prec >= 1, "problem: bad solver parameters");
   if (p.vel_off_diagonals != 0)
@@ -178,8 +196,6 @@ Ctx::Ctx(const s35_problem &p)
   // The gated alternative ilu_blocks = k cuts the owned rows into k contiguous ranges and keeps only the
   // couplings inside a range (see the header); k = 1 keeps everything.
   ilu_blocks = std::max<int32_t>(1, p.ilu_blocks);
-  if (const char *t = std::getenv("S35_ILU_BLOCKS"))
-    ilu_blocks = std::max(1, std::atoi(t));
   auto make_block = [&](const DevMatrix &A, int32_t n_own, DevMatrix &blk, DevBuf<int32_t> &src) {
     auto range_of = [&](int32_t i) { return (int32_t)((int64_t)i * ilu_blocks / n_own); };
     std::vector<int32_t> rp(n_own + 1, 0), cl, from;
@@ -260,7 +276,9 @@ Ctx::Ctx(const s35_problem &p)
   S35_CUDA(cudaStreamSynchronize(s));
 }
 
-Ctx::~Ctx()
+Ctx::~Ctx() { release_handles(); }
+
+void Ctx::release_handles()
 {
   for (auto &pd : pending)
     {
@@ -280,6 +298,15 @@ Ctx::~Ctx()
     }
   if (stream)
     cudaStreamDestroy(stream);
+  pending.clear();
+  event_pool.clear();
+  fork_event = nullptr;
+  stream = nullptr;
+  for (int d = 0; d < 3; ++d)
+    {
+      join_event[d] = nullptr;
+      comp_stream[d] = nullptr;
+    }
 }
 
 size_t Ctx::begin_section(const char *name)
@@ -456,11 +483,23 @@ void Ctx::diffusion_step(bool reinit_prec)
       {
         S35_CUDA(cudaEventRecord(fork_event, s));
         std::exception_ptr failure[3];
-        std::thread workers[3];
+        // joins whatever was started, also when starting a later thread fails
+        struct Workers
+        {
+          std::thread t[3];
+          void join()
+          {
+            for (auto &w : t)
+              if (w.joinable())
+                w.join();
+          }
+          ~Workers() { join(); }
+        } workers;
+        for (int d = 0; d < dim; ++d)
+          S35_CUDA(cudaStreamWaitEvent(comp_stream[d], fork_event, 0));
         for (int d = 0; d < dim; ++d)
           {
-            S35_CUDA(cudaStreamWaitEvent(comp_stream[d], fork_event, 0));
-            workers[d] = std::thread([this, d, reinit_prec, &failure] {
+            workers.t[d] = std::thread([this, d, reinit_prec, &failure] {
               try
                 {
                   S35_CUDA(cudaSetDevice(device));
@@ -473,8 +512,7 @@ void Ctx::diffusion_step(bool reinit_prec)
                 }
             });
           }
-        for (int d = 0; d < dim; ++d)
-          workers[d].join();
+        workers.join();
         for (int d = 0; d < dim; ++d)
           if (!failure[d])
             S35_CUDA(cudaStreamWaitEvent(s, join_event[d], 0));

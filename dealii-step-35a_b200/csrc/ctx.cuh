@@ -90,6 +90,8 @@ struct Ctx
 
   explicit Ctx(const s35_problem &p);
   ~Ctx();
+  void build(const s35_problem &p);   // the constructor's body
+  void release_handles();              // streams and events (device buffers release themselves)
   Ctx(const Ctx &) = delete;
   Ctx &operator=(const Ctx &) = delete;
 

@@ -33,7 +33,8 @@ __device__ __forceinline__ double canonical(double v) { return v != v ? __longlo
 // One warp per row.  A lane first loads its (column, value) pairs of the row into registers -- P per lane
 // and chunk, all loads in flight together -- and only then polls the solution entries it needs, all pending
 // ones together and only the pending ones, so that rows far ahead of the wave front put one request per
-// unresolved dependency and polling round on L2, with a growing pause between rounds.  The wait for the
+// unresolved dependency and polling round on L2 (an optional growing pause between rounds exists for
+// experiments; it only added latency on B200 and is off).  The wait for the
 // dependency that is produced last costs one round trip through L2 plus the warp reduction.  Every lane
 // adds its products in index order and the warp reduction is a fixed tree: the result does not depend on
 // timing.
@@ -236,7 +237,6 @@ void DevIlu::create(const DevMatrix &A, cudaStream_t s)
   const std::vector<int32_t> &rp = A.h_rowptr, &cl = A.h_col;
   std::vector<int32_t> level_f(n, 0), level_b(n, 0);
   levels_fwd = levels_bwd = n ? 1 : 0;
-  int64_t lower = 0;
   for (int32_t r = 0; r < n; ++r)
     {
       bool has_diag = false;
@@ -244,10 +244,7 @@ void DevIlu::create(const DevMatrix &A, cudaStream_t s)
       for (int32_t k = rp[r]; k < rp[r + 1]; ++k)
         {
           if (cl[k] < r)
-            {
-              lv = std::max(lv, level_f[cl[k]] + 1);
-              ++lower;
-            }
+            lv = std::max(lv, level_f[cl[k]] + 1);
           has_diag = has_diag || cl[k] == r;
         }
       S35_REQUIRE(has_diag, "ILU: every row must store its diagonal entry");
@@ -309,7 +306,6 @@ void DevIlu::create(const DevMatrix &A, cudaStream_t s)
       max_half = std::max(max_half, std::max(lo, rp[r + 1] - rp[r] - lo - 1));
     }
   per_lane = max_half <= 128 ? 2 : 4; // measured on B200: 2 beats 1 and 4 for Q1 (<= 13) and Q2 (<= ~100) rows
-  (void)lower;
   if (const char *g = std::getenv("S35_ILU_PER_LANE"))
     {
       const int v = std::atoi(g);

@@ -3,6 +3,7 @@
 #include "h5lite.h"
 
 #include <chrono>
+#include <cstdlib>
 #include <cstdio>
 #include <iomanip>
 #include <iostream>
@@ -119,6 +120,15 @@ void NavierStokesProjection<dim>::create_triangulation_and_dofs(const unsigned i
   std::cout << "height: " << height << std::endl;
 
   view.reset(new ProblemView(*disc, parameters));
+  // The parameter file is the reference's and has no entry for the gated block-ILU alternative
+  // (s35_problem.ilu_blocks); the program takes it from the environment and says so.
+  if (const char *blocks = std::getenv("S35_ILU_BLOCKS"))
+    if (std::atoi(blocks) > 1)
+      {
+        view->problem.ilu_blocks = std::atoi(blocks);
+        std::cout << "GATED ALTERNATIVE: ILU(0) of " << view->problem.ilu_blocks
+                  << " index-range blocks instead of the reference's SparseILU" << std::endl;
+      }
   check(s35_ctx_create(&view->problem, &ctx));
 
   std::cout << "dim (X_h) = " << ((long)disc->vel.n_dofs * dim) << std::endl

@@ -86,7 +86,9 @@ s35_status s35_condense(s35_matrix *A, double *rhs, int32_t n_constrained, const
  * ---------------------------------------------------------------------- */
 typedef struct s35_ilu s35_ilu;
 
-/* symbolic set-up on the pattern of A (use_previous_sparsity=true: done once) */
+/* symbolic set-up on the pattern of A (use_previous_sparsity=true: done once).  The preconditioner keeps a
+ * reference to A's pattern and works on A's stream: destroy it BEFORE A (SparseILU has the same rule for its
+ * SparsityPattern). */
 s35_status s35_ilu_create(const s35_matrix *A, s35_ilu **out);
 void s35_ilu_destroy(s35_ilu *p);
 /* SparseILU::initialize(A, AdditionalData(strengthen_diagonal, 0)): numeric factorisation,
