@@ -72,3 +72,37 @@ def rel_diff(a, b, scale=None):
 
 def seeded_vector(n, seed=35):
     return np.random.Generator(np.random.PCG64(seed)).standard_normal(n)
+
+
+def write_channel_inp(path, nx, ny, length=8.0, height=4.1):
+    """A plain channel [0, length] x [0, height] of nx x ny cells as a UCD file with the reference's boundary
+    indicators (1 walls, 2 inflow at x = 0, 3 outflow at x = length; nsbench2.inp uses the same)."""
+    vid = lambda i, j: j * (nx + 1) + i
+    lines = ["%d %d 0 0 0" % ((nx + 1) * (ny + 1), nx * ny + 2 * nx + 2 * ny)]
+    for j in range(ny + 1):
+        for i in range(nx + 1):
+            lines.append("%d %.17g %.17g 0" % (vid(i, j), length * i / nx, height * j / ny))
+    k = 1
+    for j in range(ny):
+        for i in range(nx):
+            lines.append("%d 1 quad %d %d %d %d" % (k, vid(i, j), vid(i + 1, j), vid(i + 1, j + 1), vid(i, j + 1)))
+            k += 1
+    for i in range(nx):
+        for j in (0, ny):
+            lines.append("%d 1 line %d %d" % (k, vid(i, j), vid(i + 1, j)))
+            k += 1
+    for j in range(ny):
+        for i, ident in ((0, 2), (nx, 3)):
+            lines.append("%d %d line %d %d" % (k, ident, vid(i, j), vid(i, j + 1)))
+            k += 1
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+
+
+def poiseuille(disc, reynolds, length=8.0, height=4.1, u_max=1.5):
+    """The exact steady solution the reference's inflow profile (step-35a.cc:373) belongs to in a plain channel:
+    u = (4 Um y (H - y) / H^2, 0), p = 8 Um (L - x) / (Re H^2).  Q2 / Q1 hold it exactly."""
+    y = disc.vel_support[:, 1]
+    u = [4.0 * u_max * y * (height - y) / height ** 2, np.zeros(disc.nv)]
+    p = 8.0 * u_max * (length - disc.pres_support[:, 0]) / (reynolds * height ** 2)
+    return u, p

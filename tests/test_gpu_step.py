@@ -10,7 +10,7 @@ own, stated, tolerance."""
 import numpy as np
 import pytest
 
-from conftest import rel_diff, start_state
+from conftest import poiseuille, rel_diff, run_params, start_state, write_channel_inp
 
 pytestmark = pytest.mark.gpu
 
@@ -239,3 +239,25 @@ def test_block_ilu_gated_alternative_against_the_oracle(pkg, ob, make_disc):
     start_state(pkg, disc, exact)
     exact.advance(2, 4)
     assert not np.array_equal(exact.get_field(pkg.PRES_N), orc.get_field(pkg.PRES_N))   # the option changes the solve
+
+
+@pytest.mark.parametrize("reynolds,rotational", [(100.0, 1), (10.0, 0)])
+def test_known_answer_poiseuille_flow_is_a_fixed_point(pkg, tmp_path, reynolds, rotational):
+    """The analytic known answer of tests/test_oracle.py on the device path: started from plane Poiseuille flow (an
+    exact solution that Q2/Q1 represent exactly, with the reference's inflow profile) the time loop stays on it."""
+    mesh = str(tmp_path / "channel.inp")
+    write_channel_inp(mesh, 8, 4)
+    disc = pkg.Disc(mesh, 2, run_params(pkg, reynolds=reynolds, vel_eps=1e-12, n_global_refines=1, rotational=rotational))
+    u, p = poiseuille(disc, reynolds)
+    ctx = pkg.Ctx(disc.problem)
+    for field in (pkg.U_N, pkg.U_N_MINUS_1):
+        for d in range(2):
+            ctx.set_field(field, u[d], d)
+    ctx.set_field(pkg.PRES_N, p)
+    ctx.set_field(pkg.PRES_N_MINUS_1, p)
+    ctx.advance(2, 10)
+    assert np.abs(ctx.get_field(pkg.U_N, 0) - u[0]).max() < 1e-9
+    assert np.abs(ctx.get_field(pkg.U_N, 1)).max() < 1e-9
+    assert np.abs(ctx.get_field(pkg.PRES_N) - p).max() < 1e-8 * max(1.0, np.abs(p).max())
+    assert np.abs(ctx.get_field(pkg.PHI_N)).max() < 1e-8
+    ctx.close()

@@ -9,7 +9,7 @@ import pytest
 import scipy.sparse as sp
 import scipy.sparse.linalg as spla
 
-from conftest import GOLDEN_DIR, rel_diff, run_params, seeded_vector, start_state
+from conftest import write_channel_inp, poiseuille, GOLDEN_DIR, rel_diff, run_params, seeded_vector, start_state
 
 
 def tridiagonal(n):
@@ -318,3 +318,34 @@ def test_block_ilu_alternative_in_the_oracle(pkg, ob, make_disc):
         assert not np.array_equal(a, b)
         assert np.max(np.abs(a - b)) <= 5e-6 * max(1.0, np.max(np.abs(a)))
     assert runs[1][1] >= runs[0][1]
+
+
+@pytest.mark.parametrize("reynolds,rotational", [(100.0, 1), (10.0, 1), (100.0, 0)])
+def test_known_answer_poiseuille_flow_is_a_fixed_point(pkg, ob, tmp_path, reynolds, rotational):
+    """Analytic known answer (the reference ships none): plane Poiseuille flow solves the Navier-Stokes equations with
+    the reference's inflow profile, no-slip walls and its outflow condition, and Q2/Q1 represent it exactly.  Started
+    from it, the time loop has to stay on it -- which needs the mass, stiffness, gradient and advection operators,
+    their signs, the BDF2 weights, the constraints and the pressure update all to be right."""
+    mesh = str(tmp_path / "channel.inp")
+    write_channel_inp(mesh, 8, 4)
+    params = run_params(pkg, reynolds=reynolds, vel_eps=1e-12, n_global_refines=1, rotational=rotational)
+    disc = pkg.Disc(mesh, 2, params)
+    u, p = poiseuille(disc, reynolds)
+    orc = ob.Oracle(disc.problem)
+    for field in (pkg.U_N, pkg.U_N_MINUS_1):
+        for d in range(2):
+            orc.set_field(field, u[d], d)
+    orc.set_field(pkg.PRES_N, p)
+    orc.set_field(pkg.PRES_N_MINUS_1, p)
+    orc.advance(2, 10)
+    assert np.abs(orc.get_field(pkg.U_N, 0) - u[0]).max() < 1e-9
+    assert np.abs(orc.get_field(pkg.U_N, 1)).max() < 1e-9
+    assert np.abs(orc.get_field(pkg.PRES_N) - p).max() < 1e-8 * max(1.0, np.abs(p).max())
+    assert np.abs(orc.get_field(pkg.PHI_N)).max() < 1e-8
+    # and it is not a fixed point of a wrong pressure: the same start with p = 0 moves away at once
+    orc2 = ob.Oracle(disc.problem)
+    for field in (pkg.U_N, pkg.U_N_MINUS_1):
+        for d in range(2):
+            orc2.set_field(field, u[d], d)
+    orc2.advance(2, 1)
+    assert np.abs(orc2.get_field(pkg.PHI_N)).max() > 1e-6
