@@ -1,6 +1,7 @@
 #include "sparse.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace s35 {
 
@@ -41,12 +42,99 @@ k_spmv(int32_t n_rows, const int32_t *__restrict__ rowptr, const int32_t *__rest
     y[row] = add ? y[row] + sum : sum;
 }
 
+// Warp-per-row variant with R consecutive rows of a warp in flight together: the R + 1 row boundaries come from
+// one load, then every trip issues the (col, val) loads of all R rows before the first gather of x is needed.
+// The row-per-warp kernel above is bound by its chain of dependent loads (row pointer -> col/val -> x), not by
+// bandwidth; this keeps R chains going per warp.  Per row the arithmetic is the same as in k_spmv<32, 1> -- lane
+// j adds its entries beg + j, beg + j + 32, ... in that order, then the same shuffle tree -- so the results are
+// bit-identical to it.
+template <int R>
+__global__ void __launch_bounds__(kBlock)
+k_spmv_rows(int32_t n_rows, const int32_t *__restrict__ rowptr, const int32_t *__restrict__ col, const double *__restrict__ v0,
+            const double *__restrict__ x0, double *__restrict__ y, int add)
+{
+  const int lane = threadIdx.x & 31;
+  const int64_t row0 = ((((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5)) * R;
+  if (row0 >= n_rows)
+    return;
+  const int32_t bound = rowptr[min(row0 + lane, (int64_t)n_rows)]; // lanes 0..R are used; rows past the end come out empty
+  int32_t k[R], end[R];
+  double sum[R];
+  int32_t longest = 0;
+#pragma unroll
+  for (int i = 0; i < R; ++i)
+    {
+      const int32_t beg = __shfl_sync(0xffffffffu, bound, i);
+      end[i] = __shfl_sync(0xffffffffu, bound, i + 1);
+      longest = max(longest, end[i] - beg);
+      k[i] = beg + lane;
+      sum[i] = 0.0;
+    }
+  for (int32_t done = 0; done < longest; done += 32)
+    {
+      int32_t c[R];
+      double a[R];
+#pragma unroll
+      for (int i = 0; i < R; ++i)
+        {
+          const bool in = k[i] < end[i];
+          c[i] = in ? col[k[i]] : -1;
+          a[i] = in ? v0[k[i]] : 0.0;
+        }
+#pragma unroll
+      for (int i = 0; i < R; ++i)
+        {
+          if (c[i] >= 0)
+            sum[i] += a[i] * __ldg(x0 + c[i]);
+          k[i] += 32;
+        }
+    }
+  double mine = 0.0;
+#pragma unroll
+  for (int i = 0; i < R; ++i)
+    {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1)
+        sum[i] += __shfl_down_sync(0xffffffffu, sum[i], o, 32);
+      const double total = __shfl_sync(0xffffffffu, sum[i], 0);
+      if (lane == i)
+        mine = total;
+    }
+  if (lane < R && row0 + lane < n_rows)
+    y[row0 + lane] = add ? y[row0 + lane] + mine : mine;
+}
+
+// rows in flight per warp for matrices whose rows take a whole warp (0: the plain row-per-warp kernel)
+int rows_in_flight()
+{
+  if (const char *t = std::getenv("S35_SPMV_ROWS"))
+    return std::atoi(t);
+  return 0;
+}
+
+template <int R>
+void launch_spmv_rows(int32_t n_rows, const int32_t *rowptr, const int32_t *col, const double *v, const double *x, double *y,
+                      bool add, cudaStream_t s)
+{
+  const int64_t warps = ((int64_t)n_rows + R - 1) / R;
+  const int grid = (int)((warps * 32 + kBlock - 1) / kBlock);
+  S35_LAUNCH((k_spmv_rows<R>), grid, kBlock, 0, s, n_rows, rowptr, col, v, x, y, (int)add);
+}
+
 template <int NV>
 void launch_spmv(int lanes, int32_t n_rows, const int32_t *rowptr, const int32_t *col, const double *const *v,
                  const double *const *x, double *y, bool add, cudaStream_t s)
 {
   if (n_rows == 0)
     return;
+  if (NV == 1 && lanes == 32)
+    switch (rows_in_flight())
+      {
+      case 2: launch_spmv_rows<2>(n_rows, rowptr, col, v[0], x[0], y, add, s); return;
+      case 4: launch_spmv_rows<4>(n_rows, rowptr, col, v[0], x[0], y, add, s); return;
+      case 8: launch_spmv_rows<8>(n_rows, rowptr, col, v[0], x[0], y, add, s); return;
+      default: break;
+      }
   const int64_t threads = (int64_t)n_rows * lanes;
   const int grid = (int)((threads + kBlock - 1) / kBlock);
   const double *v1 = NV > 1 ? v[1] : nullptr, *v2 = NV > 2 ? v[2] : nullptr;
