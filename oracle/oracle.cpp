@@ -14,6 +14,9 @@
 
 #ifdef _OPENMP
 #include <omp.h>
+
+#include <mutex>
+#include <thread>
 #endif
 
 namespace {
@@ -45,9 +48,22 @@ struct Csr
 
 // SparseMatrix::vmult / vmult_add: row sums in deal.II's storage order, i.e. the diagonal first (square
 // matrices), then ascending columns [A.3]
+// Threads a matrix-vector product may use.  deal.II's SparseMatrix::vmult splits its rows over the task
+// scheduler's workers wherever it is called from; here: the whole team at top level, an equal share inside the
+// per-component tasks of the diffusion step, and what the caller set for a side task.
+int g_share_in_tasks = 1;
+thread_local int t_team_override = 0;
+int team_size()
+{
+  if (t_team_override > 0)
+    return t_team_override;
+  return omp_get_level() > 0 ? g_share_in_tasks : g_threads;
+}
+
 void vmult(const Csr &P, const double *val, const double *x, double *y, bool add)
 {
-#pragma omp parallel for schedule(static) num_threads(g_threads) if (g_threads > 1)
+  const int team = team_size();
+#pragma omp parallel for schedule(static) num_threads(team) if (team > 1)
   for (int r = 0; r < P.n_rows; ++r)
     {
       double s = 0.0;
@@ -510,7 +526,13 @@ struct Timer
   const char *name;
   std::chrono::steady_clock::time_point t0;
   Timer(oracle_ctx &c_, const char *n) : c(c_), name(n), t0(std::chrono::steady_clock::now()) {}
-  ~Timer() { c.seconds[name] += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
+  ~Timer()
+  {
+    static std::mutex guard; // sections are timed from concurrent tasks
+    const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    std::lock_guard<std::mutex> lock(guard);
+    c.seconds[name] += dt;
+  }
 };
 
 // assemble_one_cell_of_advection (ref:1366-1424), written like the reference: FEValues quantities first,
@@ -922,6 +944,9 @@ int oracle_diffusion_step(oracle_ctx *c, int reinit_prec)
     {
       Timer t(*c, "solve_diffusion_component");
       std::string failure;
+      // one task per component as in the reference (ref:1277-1325); the products inside share the other threads
+      g_share_in_tasks = std::max(1, g_threads / dim);
+      omp_set_max_active_levels(2);
 #pragma omp parallel for num_threads(std::min(g_threads, dim)) if (g_threads > 1)
       for (int d = 0; d < dim; ++d)
         {
@@ -1018,11 +1043,36 @@ int oracle_advance(oracle_ctx *c, int first_n, int n_steps, int start_n, int sta
         }
       rc = rc || oracle_diffusion_step(c, (n % c->update_prec == 0) || (n == start_n));
       rc = rc || oracle_interpolate_velocity(c);
-      // the reference runs the assembly concurrently with projection + pressure update (ref:1219-1235);
-      // they touch disjoint data, so the order does not matter
-      rc = rc || oracle_assemble_advection_term(c);
-      rc = rc || oracle_projection_step(c);
-      rc = rc || oracle_update_pressure(c);
+      if (rc)
+        return rc;
+      // Two tasks as in the reference (ref:1219-1235): the assembly next to projection + pressure update.  They
+      // touch disjoint data, so the results do not depend on running them together; with one thread they run
+      // one after the other.
+      if (g_threads > 1)
+        {
+          int rc_side = 0;
+          std::string side_error; // the message lives in the task's own thread
+          std::thread side([&] {
+            t_team_override = std::min(2, g_threads);
+            rc_side = oracle_projection_step(c);
+            rc_side = rc_side ? rc_side : oracle_update_pressure(c);
+            if (rc_side)
+              side_error = g_error;
+          });
+          rc = oracle_assemble_advection_term(c);
+          side.join();
+          if (!rc && rc_side)
+            {
+              g_error = side_error;
+              rc = rc_side;
+            }
+        }
+      else
+        {
+          rc = rc || oracle_assemble_advection_term(c);
+          rc = rc || oracle_projection_step(c);
+          rc = rc || oracle_update_pressure(c);
+        }
       if (rc)
         return rc;
     }
