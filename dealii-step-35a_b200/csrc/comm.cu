@@ -1,5 +1,7 @@
 #include "comm.cuh"
 
+#include "combiner.h"
+
 #include <dlfcn.h>
 #include <nccl.h> // types only; the library is opened with dlopen
 
@@ -74,17 +76,112 @@ struct NcclApi
 
 NcclApi g_nccl;
 
+void pack_for_send(HaloDev &h, const double *x, cudaStream_t s)
+{
+  const int32_t n_send = h.empty() ? 0 : h.send_ptr.back();
+  if (n_send)
+    S35_LAUNCH(k_pack, (n_send + 255) / 256, 256, 0, s, h.send_buf.ptr, x, h.send_idx.ptr, n_send);
+}
+
+// the sends and receives of one ghost exchange; the caller opens and closes the NCCL group
+void enqueue_halo_transfers(ncclComm_t comm, HaloDev &h, double *x, cudaStream_t s)
+{
+  for (size_t q = 0; q < h.neighbor_rank.size(); ++q)
+    {
+      const int32_t ns = h.send_ptr[q + 1] - h.send_ptr[q], nr = h.recv_ptr[q + 1] - h.recv_ptr[q];
+      if (ns)
+        g_nccl.check(g_nccl.Send(h.send_buf.ptr + h.send_ptr[q], (size_t)ns, ncclDouble, h.neighbor_rank[q], comm, s), "ncclSend");
+      if (nr)
+        g_nccl.check(g_nccl.Recv(x + h.n_owned + h.recv_ptr[q], (size_t)nr, ncclDouble, h.neighbor_rank[q], comm, s), "ncclRecv");
+    }
+}
+
+// What the collective combiner (combiner.h) needs from CUDA and NCCL: every round goes out on one communication
+// stream of the one communicator, inside one NCCL group.
+struct NcclRounds
+{
+  using Stream = cudaStream_t;
+  using Event = cudaEvent_t;
+  struct Op
+  {
+    HaloDev *halo = nullptr; // a ghost exchange of x if set, else a sum of count doubles at x
+    double *x = nullptr;
+    int count = 0;
+  };
+  ncclComm_t comm = nullptr;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t party[3] = {nullptr, nullptr, nullptr}, round[2] = {nullptr, nullptr};
+  void create(ncclComm_t c)
+  {
+    comm = c;
+    S35_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    for (cudaEvent_t &e : party)
+      S35_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (cudaEvent_t &e : round)
+      S35_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  ~NcclRounds()
+  {
+    for (cudaEvent_t e : party)
+      if (e)
+        cudaEventDestroy(e);
+    for (cudaEvent_t e : round)
+      if (e)
+        cudaEventDestroy(e);
+    if (stream)
+      cudaStreamDestroy(stream);
+  }
+  Stream comm_stream() { return stream; }
+  Event party_event(int p) { return party[p]; }
+  Event round_event(int parity) { return round[parity]; }
+  void record(Event e, Stream s) { S35_CUDA(cudaEventRecord(e, s)); }
+  void wait(Stream s, Event e) { S35_CUDA(cudaStreamWaitEvent(s, e, 0)); }
+  void group_begin() { g_nccl.check(g_nccl.GroupStart(), "ncclGroupStart"); }
+  void group_end() { g_nccl.check(g_nccl.GroupEnd(), "ncclGroupEnd"); }
+  void issue(const Op &op, Stream s)
+  {
+    if (op.halo)
+      enqueue_halo_transfers(comm, *op.halo, op.x, s);
+    else
+      g_nccl.check(g_nccl.AllReduce(op.x, op.x, (size_t)op.count, ncclDouble, ncclSum, comm, s), "ncclAllReduce");
+  }
+};
+
+// one velocity component's view of the shared communicator
+struct CombinedComm : Comm
+{
+  Combiner<NcclRounds> *rounds = nullptr;
+  int party = 0;
+  void allreduce_sum(double *buf, int count, cudaStream_t s) override { rounds->submit(party, NcclRounds::Op{nullptr, buf, count}, s); }
+  void exchange(HaloDev &h, double *x, cudaStream_t s) override
+  {
+    // handed in even when this rank has nothing to exchange: all ranks have to form the same rounds
+    pack_for_send(h, x, s);
+    rounds->submit(party, NcclRounds::Op{&h, x, 0}, s);
+  }
+  void leave() override { rounds->leave(party); }
+};
+
 struct NcclComm : Comm
 {
   ncclComm_t comm = nullptr;
-  std::vector<std::unique_ptr<NcclComm>> subs;
+  std::vector<std::unique_ptr<Comm>> subs;
+  std::unique_ptr<NcclRounds> rounds_backend;
+  std::unique_ptr<Combiner<NcclRounds>> rounds;
   ~NcclComm() override
   {
     subs.clear();
+    rounds.reset();
+    rounds_backend.reset();
     if (comm)
       g_nccl.CommDestroy(comm);
   }
   Comm *sub(int i) override { return i >= 0 && i < (int)subs.size() ? subs[i].get() : nullptr; }
+  void enter_all() override
+  {
+    if (rounds)
+      rounds->enter_all();
+  }
   void allreduce_sum(double *buf, int count, cudaStream_t s) override
   {
     g_nccl.check(g_nccl.AllReduce(buf, buf, (size_t)count, ncclDouble, ncclSum, comm, s), "ncclAllReduce");
@@ -93,19 +190,26 @@ struct NcclComm : Comm
   {
     if (h.empty())
       return;
-    const int32_t n_send = h.send_ptr.back();
-    if (n_send)
-      S35_LAUNCH(k_pack, (n_send + 255) / 256, 256, 0, s, h.send_buf.ptr, x, h.send_idx.ptr, n_send);
+    pack_for_send(h, x, s);
     g_nccl.check(g_nccl.GroupStart(), "ncclGroupStart");
-    for (size_t q = 0; q < h.neighbor_rank.size(); ++q)
-      {
-        const int32_t ns = h.send_ptr[q + 1] - h.send_ptr[q], nr = h.recv_ptr[q + 1] - h.recv_ptr[q];
-        if (ns)
-          g_nccl.check(g_nccl.Send(h.send_buf.ptr + h.send_ptr[q], (size_t)ns, ncclDouble, h.neighbor_rank[q], comm, s), "ncclSend");
-        if (nr)
-          g_nccl.check(g_nccl.Recv(x + h.n_owned + h.recv_ptr[q], (size_t)nr, ncclDouble, h.neighbor_rank[q], comm, s), "ncclRecv");
-      }
+    enqueue_halo_transfers(comm, h, x, s);
     g_nccl.check(g_nccl.GroupEnd(), "ncclGroupEnd");
+  }
+  // three views of this communicator that share it through the collective combiner
+  void make_combined_subs()
+  {
+    rounds_backend.reset(new NcclRounds);
+    rounds_backend->create(comm);
+    rounds.reset(new Combiner<NcclRounds>(*rounds_backend, 3));
+    for (int i = 0; i < 3; ++i)
+      {
+        std::unique_ptr<CombinedComm> c(new CombinedComm);
+        c->rank = rank;
+        c->n_ranks = n_ranks;
+        c->rounds = rounds.get();
+        c->party = i;
+        subs.push_back(std::move(c));
+      }
   }
 };
 
@@ -255,12 +359,17 @@ void comm_init(int rank, int n_ranks, const unsigned char id[128])
   ncclUniqueId uid;
   std::memcpy(&uid, id, 128);
   g_nccl.check(g_nccl.CommInitRank(&c->comm, n_ranks, uid, rank), "ncclCommInitRank");
-  // Optionally three more communicators over the same ranks, one per velocity component, so that the
-  // components can run concurrently on a partition as they do on a single GPU.  Measured on 2 and 4 B200s
-  // this is 15-20 % faster per step, but a run on 8 GPUs dead-locked with it, so it is opt-in
-  // (S35_DIST_CONCURRENT=1) until that is understood; by default the components take turns on one communicator.
+  // Concurrent velocity components on a partition, as on a single GPU; opt-in, by default the components take
+  // turns on the one communicator.
+  //   S35_DIST_CONCURRENT=1: three more communicators over the same ranks, one per component.  Measured on 2 and
+  //     4 B200s this is 15-20 % faster per step, but a run on 8 GPUs dead-locked with it.
+  //   S35_DIST_CONCURRENT=2: the components share this communicator through the collective combiner
+  //     (combiner.h; protocol tested on the CPU, not yet run on GPUs).
   const char *conc = std::getenv("S35_DIST_CONCURRENT");
-  if (g_nccl.CommSplit && conc && std::atoi(conc) != 0)
+  const int mode = conc ? std::atoi(conc) : 0;
+  if (mode == 2)
+    c->make_combined_subs();
+  if (g_nccl.CommSplit && mode == 1)
     for (int i = 0; i < 3; ++i)
       {
         std::unique_ptr<NcclComm> sc(new NcclComm);

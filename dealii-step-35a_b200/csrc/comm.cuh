@@ -33,6 +33,11 @@ struct Comm
   // work on this one -- the velocity components, each on its own stream and host thread.  nullptr if the
   // transport has none; the callers then take turns on the main communicator.
   virtual Comm *sub(int i) { (void)i; return nullptr; }
+  // Only meaningful where the sub-communicators share this one through the collective combiner (combiner.h):
+  // enter_all() on the parent before the concurrent solves start, leave() on a sub-communicator when its
+  // solve is over (also when it failed).  No-ops everywhere else.
+  virtual void enter_all() {}
+  virtual void leave() {}
 };
 
 // the communicator s35_comm_init created for this process, or nullptr

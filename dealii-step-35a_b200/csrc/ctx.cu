@@ -497,6 +497,12 @@ void Ctx::diffusion_step(bool reinit_prec)
         } workers;
         for (int d = 0; d < dim; ++d)
           S35_CUDA(cudaStreamWaitEvent(comp_stream[d], fork_event, 0));
+        if (comm)
+          {
+            comm->enter_all();
+            for (int d = dim; d < 3; ++d) // a 2D run has no third party
+              comm->sub(d)->leave();
+          }
         for (int d = 0; d < dim; ++d)
           {
             workers.t[d] = std::thread([this, d, reinit_prec, &failure] {
@@ -509,6 +515,16 @@ void Ctx::diffusion_step(bool reinit_prec)
               catch (...)
                 {
                   failure[d] = std::current_exception();
+                }
+              try
+                {
+                  if (comp_link[d].comm)
+                    comp_link[d].comm->leave(); // the other components must not wait for this one any more
+                }
+              catch (...)
+                {
+                  if (!failure[d])
+                    failure[d] = std::current_exception();
                 }
             });
           }

@@ -1,0 +1,17 @@
+"""The collective combiner's protocol (csrc/combiner.h) on the CPU: tests/cpp/test_combiner.cpp runs 2-4 ranks of three
+solver threads each against a mock transport that matches the ranks' operations position by position."""
+import os
+import subprocess
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_combiner_protocol_forms_the_same_rounds_on_every_rank(tmp_path):
+    exe = str(tmp_path / "test_combiner")
+    env = dict(os.environ)
+    env.pop("CXX", None)
+    subprocess.run(["g++", "-std=c++17", "-O1", "-pthread", "-I", os.path.join(ROOT, "dealii-step-35a_b200", "csrc"),
+                    os.path.join(ROOT, "tests", "cpp", "test_combiner.cpp"), "-o", exe], check=True, env=env)
+    r = subprocess.run([exe, "40"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "40 runs consistent" in r.stdout
