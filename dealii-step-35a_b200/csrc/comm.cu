@@ -76,29 +76,9 @@ struct NcclApi
 
 NcclApi g_nccl;
 
-void pack_for_send(HaloDev &h, const double *x, cudaStream_t s)
-{
-  const int32_t n_send = h.empty() ? 0 : h.send_ptr.back();
-  if (n_send)
-    S35_LAUNCH(k_pack, (n_send + 255) / 256, 256, 0, s, h.send_buf.ptr, x, h.send_idx.ptr, n_send);
-}
-
-// the sends and receives of one ghost exchange; the caller opens and closes the NCCL group
-void enqueue_halo_transfers(ncclComm_t comm, HaloDev &h, double *x, cudaStream_t s)
-{
-  for (size_t q = 0; q < h.neighbor_rank.size(); ++q)
-    {
-      const int32_t ns = h.send_ptr[q + 1] - h.send_ptr[q], nr = h.recv_ptr[q + 1] - h.recv_ptr[q];
-      if (ns)
-        g_nccl.check(g_nccl.Send(h.send_buf.ptr + h.send_ptr[q], (size_t)ns, ncclDouble, h.neighbor_rank[q], comm, s), "ncclSend");
-      if (nr)
-        g_nccl.check(g_nccl.Recv(x + h.n_owned + h.recv_ptr[q], (size_t)nr, ncclDouble, h.neighbor_rank[q], comm, s), "ncclRecv");
-    }
-}
-
-// What the collective combiner (combiner.h) needs from CUDA and NCCL: every round goes out on one communication
-// stream of the one communicator, inside one NCCL group.
-struct NcclRounds
+// What the collective combiner (combiner.h) needs from CUDA and from the transport: every round goes out on one
+// communication stream of the one communicator, inside one group.
+struct RoundsBackend
 {
   using Stream = cudaStream_t;
   using Event = cudaEvent_t;
@@ -108,19 +88,20 @@ struct NcclRounds
     double *x = nullptr;
     int count = 0;
   };
-  ncclComm_t comm = nullptr;
+  Comm *transport = nullptr;
   cudaStream_t stream = nullptr;
   cudaEvent_t party[3] = {nullptr, nullptr, nullptr}, round[2] = {nullptr, nullptr};
-  void create(ncclComm_t c)
+  explicit RoundsBackend(Comm *t) : transport(t)
   {
-    comm = c;
     S35_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     for (cudaEvent_t &e : party)
       S35_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (cudaEvent_t &e : round)
       S35_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   }
-  ~NcclRounds()
+  RoundsBackend(const RoundsBackend &) = delete;
+  RoundsBackend &operator=(const RoundsBackend &) = delete;
+  ~RoundsBackend()
   {
     for (cudaEvent_t e : party)
       if (e)
@@ -136,80 +117,122 @@ struct NcclRounds
   Event round_event(int parity) { return round[parity]; }
   void record(Event e, Stream s) { S35_CUDA(cudaEventRecord(e, s)); }
   void wait(Stream s, Event e) { S35_CUDA(cudaStreamWaitEvent(s, e, 0)); }
-  void group_begin() { g_nccl.check(g_nccl.GroupStart(), "ncclGroupStart"); }
-  void group_end() { g_nccl.check(g_nccl.GroupEnd(), "ncclGroupEnd"); }
+  void group_begin() { transport->group_begin(); }
+  void group_end() { transport->group_end(); }
   void issue(const Op &op, Stream s)
   {
     if (op.halo)
-      enqueue_halo_transfers(comm, *op.halo, op.x, s);
+      transport->exchange_transfers(*op.halo, op.x, s);
     else
-      g_nccl.check(g_nccl.AllReduce(op.x, op.x, (size_t)op.count, ncclDouble, ncclSum, comm, s), "ncclAllReduce");
+      transport->allreduce_sum(op.x, op.count, s);
   }
 };
 
 // one velocity component's view of the shared communicator
 struct CombinedComm : Comm
 {
-  Combiner<NcclRounds> *rounds = nullptr;
+  Combiner<RoundsBackend> *rounds = nullptr;
   int party = 0;
-  void allreduce_sum(double *buf, int count, cudaStream_t s) override { rounds->submit(party, NcclRounds::Op{nullptr, buf, count}, s); }
+  void allreduce_sum(double *buf, int count, cudaStream_t s) override { rounds->submit(party, RoundsBackend::Op{nullptr, buf, count}, s); }
   void exchange(HaloDev &h, double *x, cudaStream_t s) override
   {
     // handed in even when this rank has nothing to exchange: all ranks have to form the same rounds
     pack_for_send(h, x, s);
-    rounds->submit(party, NcclRounds::Op{&h, x, 0}, s);
+    rounds->submit(party, RoundsBackend::Op{&h, x, 0}, s);
+  }
+  void exchange_transfers(HaloDev &, double *, cudaStream_t) override
+  {
+    throw Error(S35_ERR_INVALID, "a combined communicator is not a transport");
   }
   void leave() override { rounds->leave(party); }
 };
 
+// three views of one transport that share it through the collective combiner
+struct SharedRounds
+{
+  std::unique_ptr<RoundsBackend> backend;
+  std::unique_ptr<Combiner<RoundsBackend>> rounds;
+  std::vector<std::unique_ptr<Comm>> views;
+  void create(Comm *transport)
+  {
+    backend.reset(new RoundsBackend(transport));
+    rounds.reset(new Combiner<RoundsBackend>(*backend, 3));
+    for (int i = 0; i < 3; ++i)
+      {
+        std::unique_ptr<CombinedComm> c(new CombinedComm);
+        c->rank = transport->rank;
+        c->n_ranks = transport->n_ranks;
+        c->rounds = rounds.get();
+        c->party = i;
+        views.push_back(std::move(c));
+      }
+  }
+  void clear()
+  {
+    views.clear();
+    rounds.reset();
+    backend.reset();
+  }
+};
+
+// S35_DIST_CONCURRENT: 0 / unset = the components take turns on the communicator (default); 1 = a communicator
+// of its own per component (NCCL only; 15-20 % faster per step on 2 and 4 B200s, dead-locked on 8); 2 = the
+// components share the communicator through the collective combiner (protocol tested on the CPU, not yet run
+// on GPUs).
+int concurrent_mode()
+{
+  const char *conc = std::getenv("S35_DIST_CONCURRENT");
+  return conc ? std::atoi(conc) : 0;
+}
+
 struct NcclComm : Comm
 {
   ncclComm_t comm = nullptr;
-  std::vector<std::unique_ptr<Comm>> subs;
-  std::unique_ptr<NcclRounds> rounds_backend;
-  std::unique_ptr<Combiner<NcclRounds>> rounds;
+  std::vector<std::unique_ptr<NcclComm>> split;
+  SharedRounds shared;
   ~NcclComm() override
   {
-    subs.clear();
-    rounds.reset();
-    rounds_backend.reset();
+    split.clear();
+    shared.clear();
     if (comm)
       g_nccl.CommDestroy(comm);
   }
-  Comm *sub(int i) override { return i >= 0 && i < (int)subs.size() ? subs[i].get() : nullptr; }
+  Comm *sub(int i) override
+  {
+    if (i >= 0 && i < (int)shared.views.size())
+      return shared.views[i].get();
+    return i >= 0 && i < (int)split.size() ? split[i].get() : nullptr;
+  }
   void enter_all() override
   {
-    if (rounds)
-      rounds->enter_all();
+    if (shared.rounds)
+      shared.rounds->enter_all();
   }
   void allreduce_sum(double *buf, int count, cudaStream_t s) override
   {
     g_nccl.check(g_nccl.AllReduce(buf, buf, (size_t)count, ncclDouble, ncclSum, comm, s), "ncclAllReduce");
+  }
+  void group_begin() override { g_nccl.check(g_nccl.GroupStart(), "ncclGroupStart"); }
+  void group_end() override { g_nccl.check(g_nccl.GroupEnd(), "ncclGroupEnd"); }
+  void exchange_transfers(HaloDev &h, double *x, cudaStream_t s) override
+  {
+    for (size_t q = 0; q < h.neighbor_rank.size(); ++q)
+      {
+        const int32_t ns = h.send_ptr[q + 1] - h.send_ptr[q], nr = h.recv_ptr[q + 1] - h.recv_ptr[q];
+        if (ns)
+          g_nccl.check(g_nccl.Send(h.send_buf.ptr + h.send_ptr[q], (size_t)ns, ncclDouble, h.neighbor_rank[q], comm, s), "ncclSend");
+        if (nr)
+          g_nccl.check(g_nccl.Recv(x + h.n_owned + h.recv_ptr[q], (size_t)nr, ncclDouble, h.neighbor_rank[q], comm, s), "ncclRecv");
+      }
   }
   void exchange(HaloDev &h, double *x, cudaStream_t s) override
   {
     if (h.empty())
       return;
     pack_for_send(h, x, s);
-    g_nccl.check(g_nccl.GroupStart(), "ncclGroupStart");
-    enqueue_halo_transfers(comm, h, x, s);
-    g_nccl.check(g_nccl.GroupEnd(), "ncclGroupEnd");
-  }
-  // three views of this communicator that share it through the collective combiner
-  void make_combined_subs()
-  {
-    rounds_backend.reset(new NcclRounds);
-    rounds_backend->create(comm);
-    rounds.reset(new Combiner<NcclRounds>(*rounds_backend, 3));
-    for (int i = 0; i < 3; ++i)
-      {
-        std::unique_ptr<CombinedComm> c(new CombinedComm);
-        c->rank = rank;
-        c->n_ranks = n_ranks;
-        c->rounds = rounds.get();
-        c->party = i;
-        subs.push_back(std::move(c));
-      }
+    group_begin();
+    exchange_transfers(h, x, s);
+    group_end();
   }
 };
 
@@ -288,7 +311,15 @@ struct ThreadComm : Comm
     g->barrier(); // every rank has read every buffer
     S35_CUDA(cudaMemcpyAsync(buf, tmp.ptr, count * sizeof(double), cudaMemcpyDeviceToDevice, s));
   }
-  void exchange(HaloDev &h, double *x, cudaStream_t s) override
+  SharedRounds shared;
+  Comm *sub(int i) override { return i >= 0 && i < (int)shared.views.size() ? shared.views[i].get() : nullptr; }
+  void enter_all() override
+  {
+    if (shared.rounds)
+      shared.rounds->enter_all();
+  }
+  void exchange(HaloDev &h, double *x, cudaStream_t s) override { exchange_transfers(h, x, s); }
+  void exchange_transfers(HaloDev &h, double *x, cudaStream_t s) override
   {
     S35_CUDA(cudaStreamSynchronize(s));
     g->ptr[rank] = x;
@@ -333,6 +364,13 @@ void HaloDev::create(const s35_halo &h, int32_t n_owned_, int32_t n_local_, cuda
   send_buf.alloc((size_t)std::max<int32_t>(send_ptr.back(), 1));
 }
 
+void pack_for_send(HaloDev &h, const double *x, cudaStream_t s)
+{
+  const int32_t n_send = h.empty() ? 0 : h.send_ptr.back();
+  if (n_send)
+    S35_LAUNCH(k_pack, (n_send + 255) / 256, 256, 0, s, h.send_buf.ptr, x, h.send_idx.ptr, n_send);
+}
+
 Comm *process_comm()
 {
   if (t_thread_comm)
@@ -359,16 +397,9 @@ void comm_init(int rank, int n_ranks, const unsigned char id[128])
   ncclUniqueId uid;
   std::memcpy(&uid, id, 128);
   g_nccl.check(g_nccl.CommInitRank(&c->comm, n_ranks, uid, rank), "ncclCommInitRank");
-  // Concurrent velocity components on a partition, as on a single GPU; opt-in, by default the components take
-  // turns on the one communicator.
-  //   S35_DIST_CONCURRENT=1: three more communicators over the same ranks, one per component.  Measured on 2 and
-  //     4 B200s this is 15-20 % faster per step, but a run on 8 GPUs dead-locked with it.
-  //   S35_DIST_CONCURRENT=2: the components share this communicator through the collective combiner
-  //     (combiner.h; protocol tested on the CPU, not yet run on GPUs).
-  const char *conc = std::getenv("S35_DIST_CONCURRENT");
-  const int mode = conc ? std::atoi(conc) : 0;
+  const int mode = concurrent_mode();
   if (mode == 2)
-    c->make_combined_subs();
+    c->shared.create(c.get());
   if (g_nccl.CommSplit && mode == 1)
     for (int i = 0; i < 3; ++i)
       {
@@ -376,7 +407,7 @@ void comm_init(int rank, int n_ranks, const unsigned char id[128])
         sc->rank = rank;
         sc->n_ranks = n_ranks;
         g_nccl.check(g_nccl.CommSplit(c->comm, 0, rank, &sc->comm, nullptr), "ncclCommSplit");
-        c->subs.push_back(std::move(sc));
+        c->split.push_back(std::move(sc));
       }
   g_process_comm = std::move(c);
 }
@@ -404,6 +435,8 @@ void comm_thread_bind(int rank)
   t_thread_comm->g = g_thread_group;
   t_thread_comm->rank = rank;
   t_thread_comm->n_ranks = g_thread_group->n;
+  if (concurrent_mode() == 2)
+    t_thread_comm->shared.create(t_thread_comm.get());
 }
 
 void scalar_sqrt(double *x, cudaStream_t s) { S35_LAUNCH(k_scalar_sqrt, 1, 1, 0, s, x); }

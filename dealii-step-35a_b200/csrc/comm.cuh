@@ -33,12 +33,20 @@ struct Comm
   // work on this one -- the velocity components, each on its own stream and host thread.  nullptr if the
   // transport has none; the callers then take turns on the main communicator.
   virtual Comm *sub(int i) { (void)i; return nullptr; }
+  // The exchange in two parts for callers that bundle several operations (combiner.h): the transfers alone,
+  // after the owned values have been packed (pack_for_send), between group_begin() and group_end().
+  virtual void exchange_transfers(HaloDev &halo, double *x, cudaStream_t s) = 0;
+  virtual void group_begin() {}
+  virtual void group_end() {}
   // Only meaningful where the sub-communicators share this one through the collective combiner (combiner.h):
   // enter_all() on the parent before the concurrent solves start, leave() on a sub-communicator when its
   // solve is over (also when it failed).  No-ops everywhere else.
   virtual void enter_all() {}
   virtual void leave() {}
 };
+
+// x[send_idx] -> halo.send_buf, on stream s
+void pack_for_send(HaloDev &halo, const double *x, cudaStream_t s);
 
 // the communicator s35_comm_init created for this process, or nullptr
 Comm *process_comm();
