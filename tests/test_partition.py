@@ -19,7 +19,8 @@ def free_port():
 
 
 @pytest.mark.parametrize("mesh,dim,refines,n_ranks", [("nsbench2.s35m", 2, 2, 2), ("nsbench2.s35m", 2, 1, 3),
-                                                       ("cylinder3d.s35m", 3, 0, 4)])
+                                                       ("cylinder3d.s35m", 3, 0, 4),
+                                                       ("cylinderextruded.s35m", 3, 0, 8)])  # the bench mesh, 8 GPUs
 def test_ownership_and_halo_plans_are_consistent(pkg, make_disc, mesh, dim, refines, n_ranks):
     disc = make_disc(mesh, dim, n_global_refines=refines)
     parts = [pkg.Part(disc, n_ranks, r) for r in range(n_ranks)]
