@@ -199,11 +199,20 @@ def test_conditioning_limits_field_agreement_on_finer_meshes(pkg, ob, make_disc)
 def test_oracle_reproduces_the_golden_vectors(pkg, ob, make_disc, name):
     g = np.load(os.path.join(GOLDEN_DIR, name))
     dim, refines, steps = int(g["dim"]), int(g["refines"]), int(g["steps"])
-    disc = make_disc(str(g["mesh"]) + ".s35m", dim, n_global_refines=refines, reynolds=float(g["reynolds"]))
+    disc = make_disc(str(g["mesh"]) + ".s35m", dim, n_global_refines=refines, reynolds=float(g["reynolds"]), **golden_options(g))
     orc = ob.Oracle(disc.problem)
     start_state(pkg, disc, orc)
     orc.advance(2, steps)
+    assert [orc.solver_stats(d).iterations for d in range(dim)] == list(g["its_vel"])
     check_against_golden(pkg, disc, orc, g, 1e-8)
+
+
+def golden_options(g):
+    """solver options a fixture was made with, where they differ from parameter-file.prm's"""
+    opt = {}
+    if "rotational" in g.files:
+        opt = dict(rotational=int(g["rotational"]), vel_diag_strength=float(g["diag_strength"]), vel_update_prec=int(g["update_prec"]))
+    return opt
 
 
 def check_against_golden(pkg, disc, c, g, tol):
