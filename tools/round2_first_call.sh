@@ -1,0 +1,12 @@
+# First GPU call of the next round (one GPU, about 4 minutes of box time): everything that was written after the
+# GPU budget of round 1 ran out, each step under its own timeout, results in gpurun_out/.
+#   gpurun --timeout 400 -- 'bash tools/round2_first_call.sh'
+mkdir -p gpurun_out
+# 1. the whole parity suite, then the opt-in test of the collective combiner with ranks as threads
+timeout 120 python -m pytest tests -m gpu -q 2>&1 | tail -5 > gpurun_out/r2_pytest.log
+S35_TEST_COMBINER=1 timeout 90 python -m pytest tests/test_gpu_partition.py -m gpu -q -k combiner 2>&1 | tail -15 > gpurun_out/r2_combiner.log
+# 2. rows-in-flight SpMV: bit identity and bandwidth on the bench matrix (writes gpurun_out/tune_spmv.json)
+timeout 60 python tools/tune_spmv.py > gpurun_out/r2_tune_spmv.log 2>&1
+# 3. the default bench line (roofline, kernels, e2e, cpu_baseline)
+timeout 200 python bench.py > gpurun_out/r2_bench.json 2> gpurun_out/r2_bench.err
+tail -c 600 gpurun_out/r2_pytest.log gpurun_out/r2_combiner.log gpurun_out/r2_tune_spmv.log
