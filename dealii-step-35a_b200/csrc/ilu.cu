@@ -1,5 +1,7 @@
 #include "ilu.cuh"
 
+#include "wavefront.h"
+
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -214,6 +216,226 @@ k_ilu_factor(int32_t n, const int32_t *__restrict__ order, const int32_t *__rest
     }
 }
 
+// ---------------------------------------------------------------------------------------------- wavefront mode
+// One block per sweep: 256 consumer threads (thread i owns row i of the current tile) and one producer warp that
+// keeps kWaveStages tiles of the packed factor (wavefront.h) in flight with bulk copies.  Per tile a consumer reads
+// its row's entries and their columns' solution values from shared memory (or, for the few "far" ones, from the
+// position-ordered solution in global memory), writes its result into the window and to global memory, and meets
+// the others at a named barrier: a level costs shared-memory latency and a barrier instead of a trip through L2.
+constexpr int kWaveConsumers = 256; // = WavefrontOptions::tile_rows
+constexpr int kWaveThreads = kWaveConsumers + 32;
+constexpr int kWaveStages = 4;
+
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+  asm volatile("{\n"
+               ".reg .pred p;\n"
+               "WAVE_WAIT:\n"
+               "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+               "@p bra WAVE_DONE;\n"
+               "bra WAVE_WAIT;\n"
+               "WAVE_DONE:\n"
+               "}" ::"r"(smem_addr(bar)),
+               "r"(parity)
+               : "memory");
+}
+// global -> shared bulk copy (16-byte aligned, a multiple of 16 bytes) that reports to an mbarrier
+__device__ __forceinline__ void bulk_copy_to_shared(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst)), "l"(src),
+               "r"(bytes), "r"(smem_addr(bar))
+               : "memory");
+}
+__device__ __forceinline__ double ld_l2(const double *p)
+{
+  double v;
+  asm volatile("ld.global.cg.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+
+struct WaveArgs
+{
+  const int32_t *meta, *directory;
+  const double *values;
+  int32_t n_tiles, window, stage_meta, stage_vals;
+  const double *rhs;   // right-hand sides, indexed through the plan
+  double *by_position; // the sweep's result in position order (window overflow and the next sweep's input)
+  double *natural;     // the sweep's result by row index, or nullptr
+};
+
+template <bool FORWARD>
+__global__ void __launch_bounds__(kWaveThreads, 1) k_wave_sweep(const WaveArgs a)
+{
+  extern __shared__ __align__(16) unsigned char wave_smem[];
+  double *const window = reinterpret_cast<double *>(wave_smem);
+  double *const stage_vals = window + a.window;
+  int32_t *const stage_meta = reinterpret_cast<int32_t *>(stage_vals + (size_t)kWaveStages * a.stage_vals);
+  uint64_t *const full = reinterpret_cast<uint64_t *>(stage_meta + (size_t)kWaveStages * a.stage_meta);
+  uint64_t *const empty = full + kWaveStages;
+  const int tid = threadIdx.x;
+  if (tid == 0)
+    {
+      for (int s = 0; s < kWaveStages; ++s)
+        {
+          mbar_init(full + s, 1);
+          mbar_init(empty + s, 1);
+        }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+  __syncthreads();
+
+  if (tid >= kWaveConsumers)
+    {
+      // producer: one lane keeps the stages filled
+      if (tid == kWaveConsumers)
+        for (int t = 0; t < a.n_tiles; ++t)
+          {
+            const int s = t % kWaveStages;
+            if (t >= kWaveStages)
+              mbar_wait(empty + s, (uint32_t)((t / kWaveStages - 1) & 1));
+            const int32_t meta_off = a.directory[4 * t], meta_len = a.directory[4 * t + 1];
+            const int32_t val_off = a.directory[4 * t + 2], val_len = a.directory[4 * t + 3];
+            mbar_expect_tx(full + s, (uint32_t)meta_len * 4u + (uint32_t)val_len * 8u);
+            bulk_copy_to_shared(stage_meta + (size_t)s * a.stage_meta, a.meta + meta_off, (uint32_t)meta_len * 4u, full + s);
+            if (val_len)
+              bulk_copy_to_shared(stage_vals + (size_t)s * a.stage_vals, a.values + val_off, (uint32_t)val_len * 8u, full + s);
+          }
+      return;
+    }
+
+  // consumers
+  auto rows_of = [](const int32_t *m) { return m[0]; };
+  auto rhs_index_of = [](const int32_t *m) { return m + 4 + ((m[2] + 3) & ~3) + ((m[0] + 3) & ~3); };
+  double rhs_next = 0.0;
+  if (a.n_tiles > 0)
+    {
+      mbar_wait(full + 0, 0u);
+      if (tid < rows_of(stage_meta))
+        rhs_next = ld_l2(a.rhs + rhs_index_of(stage_meta)[tid]);
+    }
+  for (int t = 0; t < a.n_tiles; ++t)
+    {
+      const int s = t % kWaveStages;
+      const int32_t *m = stage_meta + (size_t)s * a.stage_meta; // its arrival was awaited when the right-hand sides were fetched
+      const double *v = stage_vals + (size_t)s * a.stage_vals;
+      const int32_t rows = m[0], entries = m[1], max_len = m[2], first_pos = m[3];
+      const int32_t rows_pad = (rows + 3) & ~3;
+      const int32_t *off = m + 4, *row = off + ((max_len + 3) & ~3), *len = row + 2 * rows_pad, *src = len + rows_pad;
+      const double rhs = rhs_next;
+      if (tid < rows)
+        {
+          const int32_t n_mine = len[tid];
+          double acc = 0.0;
+          for (int32_t j = 0; j < n_mine; ++j)
+            {
+              const int32_t e = off[j] + tid, where = src[e];
+              const double solved = where >= 0 ? window[where] : ld_l2(a.by_position + ~where);
+              acc = fma(v[e], solved, acc);
+            }
+          double result = rhs - acc;
+          if (!FORWARD)
+            result *= v[((entries + 1) & ~1) + tid];
+          const int32_t pos = first_pos + tid;
+          window[pos & (a.window - 1)] = result;
+          a.by_position[pos] = result;
+          if (a.natural)
+            a.natural[row[tid]] = result;
+        }
+      if (t + 1 < a.n_tiles)
+        {
+          // the next tile's right-hand sides travel while this tile finishes
+          const int s1 = (t + 1) % kWaveStages;
+          mbar_wait(full + s1, (uint32_t)(((t + 1) / kWaveStages) & 1));
+          const int32_t *m1 = stage_meta + (size_t)s1 * a.stage_meta;
+          if (tid < rows_of(m1))
+            rhs_next = ld_l2(a.rhs + rhs_index_of(m1)[tid]);
+        }
+      asm volatile("bar.sync 1, %0;" ::"n"(kWaveConsumers) : "memory"); // window complete for the next tile; stage s read
+      if (tid == 0)
+        mbar_arrive(empty + s);
+    }
+}
+
+__global__ void k_wave_gather_values(int64_t n, const int32_t *__restrict__ source, const double *__restrict__ lu,
+                                     double *__restrict__ values)
+{
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    values[i] = source[i] >= 0 ? lu[source[i]] : 0.0;
+}
+
+void wave_launch(DevIlu &p, double *dst, const double *src, cudaStream_t s)
+{
+  DevIlu::Wave &w = p.wave;
+  WaveArgs fwd{w.meta[0].ptr, w.directory[0].ptr, w.values[0].ptr, w.n_tiles[0], w.window, w.stage_meta, w.stage_vals,
+               src,           w.by_position[0].ptr, nullptr};
+  WaveArgs bwd{w.meta[1].ptr, w.directory[1].ptr, w.values[1].ptr, w.n_tiles[1], w.window, w.stage_meta, w.stage_vals,
+               w.by_position[0].ptr, w.by_position[1].ptr, dst};
+  S35_LAUNCH((k_wave_sweep<true>), 1, kWaveThreads, w.smem_bytes, s, fwd);
+  S35_LAUNCH((k_wave_sweep<false>), 1, kWaveThreads, w.smem_bytes, s, bwd);
+}
+
+// packs both sweeps of the pattern; returns false if the mode does not suit this factor
+bool wave_create(DevIlu &p, const DevMatrix &A, cudaStream_t s)
+{
+  const int32_t n = A.n_rows;
+  if (n == 0 || (double)A.nnz / n > 40.0)
+    return false; // long rows: the wide sweep streams them with many SMs, one SM cannot
+  std::vector<int32_t> diag(n);
+  for (int32_t r = 0; r < n; ++r)
+    for (int32_t k = A.h_rowptr[r]; k < A.h_rowptr[r + 1]; ++k)
+      if (A.h_col[k] == r)
+        diag[r] = k;
+  WavefrontOptions opt;
+  opt.tile_rows = kWaveConsumers;
+  opt.window = 8192;
+  if (const char *t = std::getenv("S35_WAVE_WINDOW"))
+    opt.window = std::atoi(t);
+  if (const char *t = std::getenv("S35_WAVE_TILE_ENTRIES"))
+    opt.tile_entries = std::atoi(t);
+  const WavefrontPlan F = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), true, nullptr, opt);
+  const WavefrontPlan B = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), false, F.position.data(), opt);
+  DevIlu::Wave &w = p.wave;
+  w.window = opt.window;
+  w.stages = kWaveStages;
+  w.stage_meta = round_up(std::max(F.max_meta, B.max_meta), 4);
+  w.stage_vals = round_up(std::max(std::max(F.max_values, B.max_values), 2), 2);
+  w.smem_bytes = (size_t)w.window * 8 + (size_t)kWaveStages * ((size_t)w.stage_vals * 8 + (size_t)w.stage_meta * 4) + 2 * kWaveStages * 8;
+  if (w.smem_bytes > 227 * 1024)
+    return false;
+  const WavefrontPlan *plans[2] = {&F, &B};
+  for (int d = 0; d < 2; ++d)
+    {
+      const WavefrontPlan &P = *plans[d];
+      w.n_tiles[d] = P.n_tiles;
+      w.n_values[d] = P.n_values;
+      w.far_fraction[d] = P.entries ? (double)P.far_entries / (double)P.entries : 0.0;
+      w.meta[d].upload(P.meta, s);
+      w.directory[d].upload(P.directory, s);
+      std::vector<int32_t> source(P.value_source.begin(), P.value_source.end()); // factor positions fit 32 bits (nnz is int32-indexed)
+      w.value_source[d].upload(source, s);
+      w.values[d].alloc((size_t)std::max<int64_t>(P.n_values, 2));
+      w.by_position[d].alloc(n);
+    }
+  S35_CUDA(cudaFuncSetAttribute(k_wave_sweep<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w.smem_bytes));
+  S35_CUDA(cudaFuncSetAttribute(k_wave_sweep<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w.smem_bytes));
+  w.on = true;
+  return true;
+}
+
 template <int P>
 void launch_apply(DevIlu &p, double *dst, const double *src, cudaStream_t s)
 {
@@ -319,6 +541,10 @@ void DevIlu::create(const DevMatrix &A, cudaStream_t s)
   if (const char *g = std::getenv("S35_ILU_BACKOFF_NS"))
     backoff_ns = std::max(0, std::min(10000, std::atoi(g)));
   factored = false;
+  wave = Wave();
+  if (const char *mode = std::getenv("S35_ILU_MODE"))
+    if (std::strcmp(mode, "wavefront") == 0)
+      wave_create(*this, A, s);
 }
 
 void DevIlu::factor(const double *values, double strengthen_diagonal, cudaStream_t s)
@@ -333,6 +559,13 @@ void DevIlu::factor(const double *values, double strengthen_diagonal, cudaStream
   constexpr int ROWS = kBlock / 32;
   S35_LAUNCH(k_ilu_factor, (n + ROWS - 1) / ROWS, kBlock, 0, s, n, order_fwd.ptr, A.rowptr.ptr, A.diag.ptr, A.col.ptr, lu.ptr,
              ready.ptr, tickets.ptr);
+  if (wave.on)
+    for (int d = 0; d < 2; ++d)
+      if (wave.n_values[d])
+        {
+          const int grid = (int)std::min<int64_t>((wave.n_values[d] + 255) / 256, (int64_t)sm_count() * 8);
+          S35_LAUNCH(k_wave_gather_values, grid, 256, 0, s, wave.n_values[d], wave.value_source[d].ptr, lu.ptr, wave.values[d].ptr);
+        }
   factored = true;
 }
 
@@ -351,6 +584,11 @@ void DevIlu::apply(double *dst, const double *src, cudaStream_t s)
   S35_REQUIRE(dst != src, "ILU: dst must not alias src");
   if (n == 0)
     return;
+  if (wave.on)
+    {
+      wave_launch(*this, dst, src, s);
+      return;
+    }
   switch (per_lane)
     {
     case 1: launch_apply<1>(*this, dst, src, s); break;

@@ -32,6 +32,20 @@ struct DevIlu
   int backoff_ns = 0;                 // longest pause between polling rounds of a waiting row
   bool factored = false;
 
+  // Wavefront mode (S35_ILU_MODE=wavefront, off by default, for factors with short rows): the sweep runs in ONE
+  // block that walks the dependency levels in order with the recent solution values in shared memory
+  // (wavefront.h).  Index 0: forward sweep, 1: backward sweep.
+  struct Wave
+  {
+    bool on = false;
+    int32_t n_tiles[2] = {0, 0}, window = 0, stage_meta = 0, stage_vals = 0, stages = 0;
+    size_t smem_bytes = 0;
+    int64_t n_values[2] = {0, 0};
+    DevBuf<int32_t> meta[2], directory[2], value_source[2];
+    DevBuf<double> values[2], by_position[2];
+    double far_fraction[2] = {0., 0.};
+  } wave;
+
   void create(const DevMatrix &A, cudaStream_t s);
   // lu = values (+ strengthen * sum|offdiag| on the diagonal), then factorise
   void factor(const double *values, double strengthen_diagonal, cudaStream_t s);

@@ -32,6 +32,9 @@ VARIANT_SETS = {
     "default": [{}],
     "multi": [{}] + [{"S35_ILU_PER_LANE": str(p)} for p in (1, 2, 4)] + [{"S35_ILU_BLOCKS_PER_SM": str(b)} for b in (1, 2, 8)]
              + [{"S35_ILU_BACKOFF_NS": str(ns)} for ns in (32, 256)] + [{"S35_ILU_ORDER": "natural"}],
+    # one block per sweep walking the levels with the recent solution values in shared memory (pressure factor only)
+    "wavefront": [{}, {"S35_ILU_MODE": "wavefront"}, {"S35_ILU_MODE": "wavefront", "S35_WAVE_WINDOW": "16384"},
+                  {"S35_ILU_MODE": "wavefront", "S35_WAVE_TILE_ENTRIES": "3072"}],
 }
 
 
