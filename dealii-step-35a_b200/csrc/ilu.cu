@@ -339,11 +339,28 @@ __global__ void __launch_bounds__(kWaveThreads, 1) k_wave_sweep(const WaveArgs a
         {
           const int32_t n_mine = len[tid];
           double acc = 0.0;
-          for (int32_t j = 0; j < n_mine; ++j)
+          // eight entries at a time: all their loads are issued before the first product is needed; the products
+          // are still added in ascending column order into the one accumulator
+          for (int32_t j0 = 0; j0 < n_mine; j0 += 8)
             {
-              const int32_t e = off[j] + tid, where = src[e];
-              const double solved = where >= 0 ? window[where] : ld_l2(a.by_position + ~where);
-              acc = fma(v[e], solved, acc);
+              int32_t where[8];
+              double factor[8], solved[8];
+#pragma unroll
+              for (int u = 0; u < 8; ++u)
+                if (j0 + u < n_mine)
+                  {
+                    const int32_t e = off[j0 + u] + tid;
+                    where[u] = src[e];
+                    factor[u] = v[e];
+                  }
+#pragma unroll
+              for (int u = 0; u < 8; ++u)
+                if (j0 + u < n_mine)
+                  solved[u] = where[u] >= 0 ? window[where[u]] : ld_l2(a.by_position + ~where[u]);
+#pragma unroll
+              for (int u = 0; u < 8; ++u)
+                if (j0 + u < n_mine)
+                  acc = fma(factor[u], solved[u], acc);
             }
           double result = rhs - acc;
           if (!FORWARD)
