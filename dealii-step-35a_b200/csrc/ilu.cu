@@ -299,20 +299,34 @@ __global__ void __launch_bounds__(kWaveThreads, 1) k_wave_sweep(const WaveArgs a
 
   if (tid >= kWaveConsumers)
     {
-      // producer: one lane keeps the stages filled
-      if (tid == kWaveConsumers)
-        for (int t = 0; t < a.n_tiles; ++t)
-          {
-            const int s = t % kWaveStages;
-            if (t >= kWaveStages)
-              mbar_wait(empty + s, (uint32_t)((t / kWaveStages - 1) & 1));
-            const int32_t meta_off = a.directory[4 * t], meta_len = a.directory[4 * t + 1];
-            const int32_t val_off = a.directory[4 * t + 2], val_len = a.directory[4 * t + 3];
-            mbar_expect_tx(full + s, (uint32_t)meta_len * 4u + (uint32_t)val_len * 8u);
-            bulk_copy_to_shared(stage_meta + (size_t)s * a.stage_meta, a.meta + meta_off, (uint32_t)meta_len * 4u, full + s);
-            if (val_len)
-              bulk_copy_to_shared(stage_vals + (size_t)s * a.stage_vals, a.values + val_off, (uint32_t)val_len * 8u, full + s);
-          }
+      // producer warp: lane 0 keeps the stages filled.  The tile directory is read 32 tiles at a time by the whole
+      // warp, the next batch while the current one is being issued, so that the producer never waits for it.
+      const int lane = tid - kWaveConsumers;
+      const int4 *const directory = reinterpret_cast<const int4 *>(a.directory);
+      int4 next = lane < a.n_tiles ? directory[lane] : make_int4(0, 0, 0, 0);
+      for (int base = 0; base < a.n_tiles; base += 32)
+        {
+          const int4 batch = next;
+          const int ahead = base + 32 + lane;
+          next = ahead < a.n_tiles ? directory[ahead] : make_int4(0, 0, 0, 0);
+          const int count = min(32, a.n_tiles - base);
+          for (int u = 0; u < count; ++u)
+            {
+              const int32_t meta_off = __shfl_sync(0xffffffffu, batch.x, u), meta_len = __shfl_sync(0xffffffffu, batch.y, u);
+              const int32_t val_off = __shfl_sync(0xffffffffu, batch.z, u), val_len = __shfl_sync(0xffffffffu, batch.w, u);
+              if (lane == 0)
+                {
+                  const int t = base + u, s = t % kWaveStages;
+                  if (t >= kWaveStages)
+                    mbar_wait(empty + s, (uint32_t)((t / kWaveStages - 1) & 1));
+                  mbar_expect_tx(full + s, (uint32_t)meta_len * 4u + (uint32_t)val_len * 8u);
+                  bulk_copy_to_shared(stage_meta + (size_t)s * a.stage_meta, a.meta + meta_off, (uint32_t)meta_len * 4u, full + s);
+                  if (val_len)
+                    bulk_copy_to_shared(stage_vals + (size_t)s * a.stage_vals, a.values + val_off, (uint32_t)val_len * 8u, full + s);
+                }
+              __syncwarp();
+            }
+        }
       return;
     }
 
