@@ -367,6 +367,8 @@ def main():
                        "cells": disc.n_cells,
                        "preconditioner": "ILU(0) as the reference's SparseILU" if args.ilu_blocks <= 1 else
                                          "GATED ALTERNATIVE: ILU(0) of %d index-range blocks" % args.ilu_blocks,
+                       # every S35_* switch that was set: a line measured with a non-default path says so
+                       "switches": {k: v for k, v in sorted(os.environ.items()) if k.startswith("S35_")},
                        "parallelism": ("mesh partition x%d (coordinate bisection, NCCL ghost exchange + all-reduce, "
                                        "block-local ILU(0))" % world) if world > 1 else "single GPU",
                        "l2": "working set (%.0f MB of matrices) exceeds L2; kernel benchmarks flush L2 between launches"
