@@ -11,7 +11,7 @@ WANTED = [
     ("time us", "gpu__time_duration.sum", 1e-3),                      # ns in the raw page
     ("dram rd MB", "dram__bytes_read.sum", 1e-6),
     ("dram wr MB", "dram__bytes_write.sum", 1e-6),
-    ("dram %", "dram__throughput.avg.pct_of_peak_sustained_elapsed", 1.0),
+    ("dram GB/s", "dram__bytes.sum.per_second", 1.0),
     ("L2 hit %", "lts__t_sector_hit_rate.pct", 1.0),
     ("warps act %", "sm__warps_active.avg.pct_of_peak_sustained_active", 1.0),
     ("issue %", "sm__inst_issued.avg.pct_of_peak_sustained_active", 1.0),
@@ -56,6 +56,8 @@ def main():
                 if v is not None and units is not None and label.startswith("dram") and label.endswith("MB"):
                     unit = units[c].strip().lower()
                     v *= {"byte": 1.0, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}.get(unit, 1.0)
+                if v is not None and units is not None and label == "dram GB/s":
+                    v *= {"byte/s": 1e-9, "kbyte/s": 1e-6, "mbyte/s": 1e-3, "gbyte/s": 1.0, "tbyte/s": 1e3}.get(units[c].strip().lower(), 1.0)
                 cells.append(("%.2f" % (v * scale)).rjust(11) if v is not None else "-".rjust(11))
             grid = r[header.index("Grid Size")].replace(" ", "") + " x " + r[header.index("Block Size")].replace(" ", "")
             print("  " + " | ".join([r[name_col][:34].ljust(34), grid[:16].ljust(16)] + cells))
