@@ -56,6 +56,36 @@ Csr grid_pattern(int nx, int ny, int nz, int reach, const std::vector<int32_t> &
   return A;
 }
 
+// random band pattern with rows of very different lengths (some hold only their diagonal)
+Csr random_band(int32_t n, int reach, int max_per_row, std::mt19937 &rng)
+{
+  Csr A;
+  A.n = n;
+  A.rowptr.assign(1, 0);
+  A.diag.resize(n);
+  std::uniform_real_distribution<double> u(-1.0, 1.0);
+  for (int32_t r = 0; r < n; ++r)
+    {
+      std::set<int32_t> cols{r};
+      const int want = (int)(rng() % (unsigned)(max_per_row + 1));
+      for (int k = 0; k < want; ++k)
+        {
+          const int32_t c = r - reach + (int32_t)(rng() % (unsigned)(2 * reach + 1));
+          if (c >= 0 && c < n)
+            cols.insert(c);
+        }
+      for (int32_t c : cols)
+        {
+          if (c == r)
+            A.diag[r] = (int32_t)A.col.size();
+          A.col.push_back(c);
+          A.val.push_back(c == r ? 1.0 / (3.0 + u(rng)) : 0.2 * u(rng));
+        }
+      A.rowptr.push_back((int32_t)A.col.size());
+    }
+  return A;
+}
+
 bool same_bits(const std::vector<double> &a, const std::vector<double> &b)
 {
   return a.size() == b.size() && std::memcmp(a.data(), b.data(), a.size() * sizeof(double)) == 0;
@@ -160,6 +190,13 @@ int main()
     const Csr D = grid_pattern(50, 1, 1, 0, identity(50), rng); // diagonal matrix: one level, no entries
     bad |= check("diagonal of 50", D, tiny_tiles, rng);
   }
+  for (int round = 0; round < 3; ++round)
+    {
+      const Csr A = random_band(1500 + 371 * round, 150 + 400 * round, 6 + 10 * round, rng);
+      bad |= check("random band", A, standard, rng);
+      bad |= check("  window 64", A, tiny_window, rng);
+      bad |= check("  tiles 8 rows / 40 entries", A, tiny_tiles, rng);
+    }
   try
     {
       s35::WavefrontOptions wrong;
