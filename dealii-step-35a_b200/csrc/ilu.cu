@@ -435,17 +435,32 @@ bool wave_create(DevIlu &p, const DevMatrix &A, cudaStream_t s)
   opt.window = 8192;
   if (const char *t = std::getenv("S35_WAVE_WINDOW"))
     opt.window = std::atoi(t);
+  // Tiles as large as the shared memory allows: on the r1 pressure factor 3072 entries per tile give one tile per
+  // level (1 758 tiles for 1 755 levels), 1536 entries split a quarter of the levels (2 402 tiles).
+  std::vector<int> candidates = {3072, 1536, 768};
   if (const char *t = std::getenv("S35_WAVE_TILE_ENTRIES"))
-    opt.tile_entries = std::atoi(t);
-  const WavefrontPlan F = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), true, nullptr, opt);
-  const WavefrontPlan B = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), false, F.position.data(), opt);
+    candidates.assign(1, std::atoi(t));
   DevIlu::Wave &w = p.wave;
-  w.window = opt.window;
-  w.stages = kWaveStages;
-  w.stage_meta = round_up(std::max(F.max_meta, B.max_meta), 4);
-  w.stage_vals = round_up(std::max(std::max(F.max_values, B.max_values), 2), 2);
-  w.smem_bytes = (size_t)w.window * 8 + (size_t)kWaveStages * ((size_t)w.stage_vals * 8 + (size_t)w.stage_meta * 4) + 2 * kWaveStages * 8;
-  if (w.smem_bytes > 227 * 1024)
+  WavefrontPlan F, B;
+  bool fits = false;
+  for (int tile_entries : candidates)
+    {
+      opt.tile_entries = tile_entries;
+      F = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), true, nullptr, opt);
+      // the backward sweep takes its right-hand sides from the forward sweep's position-ordered result
+      B = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), false, F.position.data(), opt);
+      w.window = opt.window;
+      w.stages = kWaveStages;
+      w.stage_meta = round_up(std::max(F.max_meta, B.max_meta), 4);
+      w.stage_vals = round_up(std::max(std::max(F.max_values, B.max_values), 2), 2);
+      w.smem_bytes = (size_t)w.window * 8 + (size_t)kWaveStages * ((size_t)w.stage_vals * 8 + (size_t)w.stage_meta * 4) + 2 * kWaveStages * 8;
+      if (w.smem_bytes <= 227 * 1024)
+        {
+          fits = true;
+          break;
+        }
+    }
+  if (!fits)
     return false;
   const WavefrontPlan *plans[2] = {&F, &B};
   for (int d = 0; d < 2; ++d)

@@ -34,7 +34,7 @@ VARIANT_SETS = {
              + [{"S35_ILU_BACKOFF_NS": str(ns)} for ns in (32, 256)] + [{"S35_ILU_ORDER": "natural"}],
     # one block per sweep walking the levels with the recent solution values in shared memory (pressure factor only)
     "wavefront": [{}, {"S35_ILU_MODE": "wavefront"}, {"S35_ILU_MODE": "wavefront", "S35_WAVE_WINDOW": "16384"},
-                  {"S35_ILU_MODE": "wavefront", "S35_WAVE_TILE_ENTRIES": "3072"}],
+                  {"S35_ILU_MODE": "wavefront", "S35_WAVE_TILE_ENTRIES": "1536"}],
 }
 
 
