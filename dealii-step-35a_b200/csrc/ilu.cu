@@ -252,6 +252,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
                "r"(parity)
                : "memory");
 }
+// one attempt; its latency overlaps with whatever the thread does until it looks at the answer
+__device__ __forceinline__ uint32_t mbar_try(uint64_t *bar, uint32_t parity)
+{
+  uint32_t done;
+  asm volatile("{\n"
+               ".reg .pred p;\n"
+               "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+               "selp.u32 %0, 1, 0, p;\n"
+               "}"
+               : "=r"(done)
+               : "r"(smem_addr(bar)), "r"(parity)
+               : "memory");
+  return done;
+}
 // global -> shared bulk copy (16-byte aligned, a multiple of 16 bytes) that reports to an mbarrier
 __device__ __forceinline__ void bulk_copy_to_shared(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
 {
@@ -349,6 +363,10 @@ __global__ void __launch_bounds__(kWaveThreads, 1) k_wave_sweep(const WaveArgs a
       const int32_t rows_pad = (rows + 3) & ~3;
       const int32_t *off = m + 4, *row = off + ((max_len + 3) & ~3), *len = row + 2 * rows_pad, *src = len + rows_pad;
       const double rhs = rhs_next;
+      // the next tile's stage has normally been complete for a long time: ask now, look at the answer after the row
+      const int s1 = (t + 1) % kWaveStages;
+      const uint32_t parity1 = (uint32_t)(((t + 1) / kWaveStages) & 1);
+      const uint32_t next_landed = t + 1 < a.n_tiles ? mbar_try(full + s1, parity1) : 1u;
       if (tid < rows)
         {
           const int32_t n_mine = len[tid];
@@ -388,8 +406,8 @@ __global__ void __launch_bounds__(kWaveThreads, 1) k_wave_sweep(const WaveArgs a
       if (t + 1 < a.n_tiles)
         {
           // the next tile's right-hand sides travel while this tile finishes
-          const int s1 = (t + 1) % kWaveStages;
-          mbar_wait(full + s1, (uint32_t)(((t + 1) / kWaveStages) & 1));
+          if (!next_landed)
+            mbar_wait(full + s1, parity1);
           const int32_t *m1 = stage_meta + (size_t)s1 * a.stage_meta;
           if (tid < rows_of(m1))
             rhs_next = ld_l2(a.rhs + rhs_index_of(m1)[tid]);
