@@ -345,72 +345,42 @@ __global__ void __launch_bounds__(kWaveThreads, 1) k_wave_sweep(const WaveArgs a
     }
 
   // consumers
-  auto rows_of = [](const int32_t *m) { return m[0]; };
-  auto rhs_index_of = [](const int32_t *m) { return m + 4 + ((m[2] + 3) & ~3) + ((m[0] + 3) & ~3); };
   double rhs_next = 0.0;
   if (a.n_tiles > 0)
     {
       mbar_wait(full + 0, 0u);
-      if (tid < rows_of(stage_meta))
-        rhs_next = ld_l2(a.rhs + rhs_index_of(stage_meta)[tid]);
+      const WaveTile first = wave_tile(stage_meta, stage_vals);
+      if (tid < first.rows)
+        rhs_next = ld_l2(a.rhs + first.rhs[tid]);
     }
   for (int t = 0; t < a.n_tiles; ++t)
     {
       const int s = t % kWaveStages;
-      const int32_t *m = stage_meta + (size_t)s * a.stage_meta; // its arrival was awaited when the right-hand sides were fetched
-      const double *v = stage_vals + (size_t)s * a.stage_vals;
-      const int32_t rows = m[0], entries = m[1], max_len = m[2], first_pos = m[3];
-      const int32_t rows_pad = (rows + 3) & ~3;
-      const int32_t *off = m + 4, *row = off + ((max_len + 3) & ~3), *len = row + 2 * rows_pad, *src = len + rows_pad;
+      // the stage's arrival was awaited when its right-hand sides were fetched
+      const WaveTile tile = wave_tile(stage_meta + (size_t)s * a.stage_meta, stage_vals + (size_t)s * a.stage_vals);
       const double rhs = rhs_next;
       // the next tile's stage has normally been complete for a long time: ask now, look at the answer after the row
       const int s1 = (t + 1) % kWaveStages;
       const uint32_t parity1 = (uint32_t)(((t + 1) / kWaveStages) & 1);
       const uint32_t next_landed = t + 1 < a.n_tiles ? mbar_try(full + s1, parity1) : 1u;
-      if (tid < rows)
+      if (tid < tile.rows)
         {
-          const int32_t n_mine = len[tid];
-          double acc = 0.0;
-          // eight entries at a time: all their loads are issued before the first product is needed; the products
-          // are still added in ascending column order into the one accumulator
-          for (int32_t j0 = 0; j0 < n_mine; j0 += 8)
-            {
-              int32_t where[8];
-              double factor[8], solved[8];
-#pragma unroll
-              for (int u = 0; u < 8; ++u)
-                if (j0 + u < n_mine)
-                  {
-                    const int32_t e = off[j0 + u] + tid;
-                    where[u] = src[e];
-                    factor[u] = v[e];
-                  }
-#pragma unroll
-              for (int u = 0; u < 8; ++u)
-                if (j0 + u < n_mine)
-                  solved[u] = where[u] >= 0 ? window[where[u]] : ld_l2(a.by_position + ~where[u]);
-#pragma unroll
-              for (int u = 0; u < 8; ++u)
-                if (j0 + u < n_mine)
-                  acc = fma(factor[u], solved[u], acc);
-            }
-          double result = rhs - acc;
-          if (!FORWARD)
-            result *= v[((entries + 1) & ~1) + tid];
-          const int32_t pos = first_pos + tid;
+          const double result =
+            wave_row(tile, tid, rhs, window, WaveFarLoad{a.by_position}, FORWARD);
+          const int32_t pos = tile.first_pos + tid;
           window[pos & (a.window - 1)] = result;
           a.by_position[pos] = result;
           if (a.natural)
-            a.natural[row[tid]] = result;
+            a.natural[tile.row[tid]] = result;
         }
       if (t + 1 < a.n_tiles)
         {
           // the next tile's right-hand sides travel while this tile finishes
           if (!next_landed)
             mbar_wait(full + s1, parity1);
-          const int32_t *m1 = stage_meta + (size_t)s1 * a.stage_meta;
-          if (tid < rows_of(m1))
-            rhs_next = ld_l2(a.rhs + rhs_index_of(m1)[tid]);
+          const WaveTile next = wave_tile(stage_meta + (size_t)s1 * a.stage_meta, stage_vals + (size_t)s1 * a.stage_vals);
+          if (tid < next.rows)
+            rhs_next = ld_l2(a.rhs + next.rhs[tid]);
         }
       asm volatile("bar.sync 1, %0;" ::"n"(kWaveConsumers) : "memory"); // window complete for the next tile; stage s read
       if (tid == 0)

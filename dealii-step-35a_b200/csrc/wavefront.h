@@ -60,6 +60,91 @@ struct WavefrontPlan
 
 inline int32_t round_up(int32_t x, int32_t m) { return (x + m - 1) / m * m; }
 
+#if defined(__CUDACC__)
+#define S35_WAVE_INLINE __host__ __device__ __forceinline__
+#else
+#define S35_WAVE_INLINE inline
+#endif
+
+// A tile as it lies in the two streams (or in a stage of shared memory).  The kernel and the CPU walk below use
+// these two functions, so the index arithmetic and the order of the operations of the kernel are what the CPU
+// test exercises.
+struct WaveTile
+{
+  int32_t rows, entries, max_len, first_pos;
+  const int32_t *off, *row, *rhs, *len, *src;
+  const double *val, *piv;
+};
+
+S35_WAVE_INLINE WaveTile wave_tile(const int32_t *m, const double *v)
+{
+  WaveTile t;
+  t.rows = m[0];
+  t.entries = m[1];
+  t.max_len = m[2];
+  t.first_pos = m[3];
+  const int32_t rows_pad = (t.rows + 3) & ~3;
+  t.off = m + 4;
+  t.row = t.off + ((t.max_len + 3) & ~3);
+  t.rhs = t.row + rows_pad;
+  t.len = t.rhs + rows_pad;
+  t.src = t.len + rows_pad;
+  t.val = v;
+  t.piv = v + ((t.entries + 1) & ~1);
+  return t;
+}
+
+// reads a solution value that has left the window from the position-ordered array; on the device through L2
+// (the value was stored by another thread of the block, long ago)
+struct WaveFarLoad
+{
+  const double *by_position;
+  S35_WAVE_INLINE double operator()(int32_t pos) const
+  {
+#if defined(__CUDA_ARCH__)
+    double v;
+    asm volatile("ld.global.cg.f64 %0, [%1];" : "=d"(v) : "l"(by_position + pos) : "memory");
+    return v;
+#else
+    return by_position[pos];
+#endif
+  }
+};
+
+// Row i of the tile: rhs - sum_j val_j * solution(column_j), times the inverse pivot in the backward sweep.  Eight
+// entries at a time, all their loads issued before the first product is needed; the products are added in
+// ascending column order into one accumulator.  far(position) reads a value that has left the window.
+S35_WAVE_INLINE double wave_row(const WaveTile &t, int32_t i, double rhs, const double *window, WaveFarLoad far, bool forward)
+{
+  const int32_t n_mine = t.len[i];
+  double acc = 0.0;
+  for (int32_t j0 = 0; j0 < n_mine; j0 += 8)
+    {
+      int32_t where[8];
+      double factor[8], solved[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (j0 + u < n_mine)
+          {
+            const int32_t e = t.off[j0 + u] + i;
+            where[u] = t.src[e];
+            factor[u] = t.val[e];
+          }
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (j0 + u < n_mine)
+          solved[u] = where[u] >= 0 ? window[where[u]] : far(~where[u]);
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (j0 + u < n_mine)
+          acc = fma(factor[u], solved[u], acc);
+    }
+  double result = rhs - acc;
+  if (!forward)
+    result *= t.piv[i];
+  return result;
+}
+
 // rowptr/col: CSR with ascending columns; diag[r]: position of the diagonal entry of row r.
 // forward: the strictly lower part (unit diagonal); backward: the strictly upper part and the pivot at diag[r].
 // rhs_index: for every row the index of its right-hand side in the vector the sweep reads (nullptr: the row index).
@@ -210,29 +295,15 @@ inline void wavefront_apply_host(const WavefrontPlan &P, const double *values, c
   std::vector<double> window(P.window, 0.0);
   for (int32_t t = 0; t < P.n_tiles; ++t)
     {
-      const int32_t *m = P.meta.data() + P.directory[4 * t];
-      const double *v = values + P.directory[4 * t + 2];
-      const int32_t rows = m[0], entries = m[1], max_len = m[2], first_pos = m[3];
-      const int32_t off_pad = round_up(max_len, 4), rows_pad4 = round_up(rows, 4);
-      const int32_t *off = m + 4, *row = off + off_pad, *rhs_idx = row + rows_pad4, *len = rhs_idx + rows_pad4, *src = len + rows_pad4;
-      const double *piv = v + round_up(entries, 2);
-      for (int32_t i = rows - 1; i >= 0; --i)
+      const WaveTile tile = wave_tile(P.meta.data() + P.directory[4 * t], values + P.directory[4 * t + 2]);
+      for (int32_t i = tile.rows - 1; i >= 0; --i)
         {
-          double acc = 0.0;
-          for (int32_t j = 0; j < len[i]; ++j)
-            {
-              const int32_t e = off[j] + i, s = src[e];
-              const double yv = s >= 0 ? window[s] : by_position[~s];
-              acc = std::fma(v[e], yv, acc);
-            }
-          double res = rhs[rhs_idx[i]] - acc;
-          if (!P.forward)
-            res *= piv[i];
-          const int32_t pos = first_pos + i;
+          const double res = wave_row(tile, i, rhs[tile.rhs[i]], window.data(), WaveFarLoad{by_position}, P.forward);
+          const int32_t pos = tile.first_pos + i;
           window[pos & (P.window - 1)] = res;
           by_position[pos] = res;
           if (natural)
-            natural[row[i]] = res;
+            natural[tile.row[i]] = res;
         }
     }
 }
