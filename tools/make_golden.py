@@ -20,7 +20,9 @@ import oracle_np  # noqa: E402
 CASES = [("nsbench2", 2, 0, 8, 100.0, {}), ("nsbench2", 2, 1, 5, 100.0, {}), ("cylinder3d", 3, 0, 2, 20.0, {}),
          # the other branches of the time loop: standard (non-rotational) pressure update, strengthened ILU diagonal,
          # preconditioner refreshed every 3 steps
-         ("nsbench2", 2, 1, 7, 100.0, {"rotational": 0, "diag_strength": 0.01, "update_prec": 3})]
+         ("nsbench2", 2, 1, 7, 100.0, {"rotational": 0, "diag_strength": 0.01, "update_prec": 3}),
+         # the bench mesh itself (unrefined: 21 190 cells, 0.57 M DoF), first two steps
+         ("cylinderextruded", 3, 0, 2, 100.0, {})]
 
 
 def main():
