@@ -182,8 +182,8 @@ def test_simulation_driver_runs_like_the_reference_loop(pkg, ob, make_disc, tmp_
 
 
 GOLDEN_TOL = {"nsbench2_r0_steps8.npz": 1e-8, "nsbench2_r1_steps5.npz": 5e-8, "cylinder3d_r0_steps2.npz": 1e-8,
-              "nsbench2_r1_steps7_variant.npz": 2e-7,
-              "cylinderextruded_r0_steps2.npz": 5e-7}   # r1: conditioning-limited like the 1e-7 of the variant test above
+              "nsbench2_r1_steps7_variant.npz": 2e-7,    # r1: conditioning-limited like the 1e-7 of the variant test above
+              "cylinderextruded_r0_steps2.npz": 5e-7}    # 0.57 M DoF: stated looser for the same reason
 
 
 @pytest.mark.parametrize("name", sorted(GOLDEN_TOL))
