@@ -44,8 +44,12 @@ def main():
     for v in variants:
         env = dict(os.environ)
         env.update(v)
-        r = subprocess.run([sys.executable, "-c", CHILD, mesh, dim, refines], env=env, capture_output=True, text=True,
-                           timeout=600)
+        try:
+            r = subprocess.run([sys.executable, "-c", CHILD, mesh, dim, refines], env=env, capture_output=True, text=True,
+                               timeout=int(os.environ.get("S35_TUNE_TIMEOUT", "90")))
+        except subprocess.TimeoutExpired:
+            print(json.dumps(v), "TIMED OUT (hung kernel?)", flush=True)
+            continue
         print(json.dumps(v), r.stdout.strip() or r.stderr[-800:], flush=True)
 
 
