@@ -217,14 +217,24 @@ k_ilu_factor(int32_t n, const int32_t *__restrict__ order, const int32_t *__rest
 }
 
 // ---------------------------------------------------------------------------------------------- wavefront mode
-// One block per sweep: 256 consumer threads (thread i owns row i of the current tile) and one producer warp that
-// keeps kWaveStages tiles of the packed factor (wavefront.h) in flight with bulk copies.  Per tile a consumer reads
-// its row's entries and their columns' solution values from shared memory (or, for the few "far" ones, from the
-// position-ordered solution in global memory), writes its result into the window and to global memory, and meets
-// the others at a named barrier: a level costs shared-memory latency and a barrier instead of a trip through L2.
-constexpr int kWaveConsumers = 256; // = WavefrontOptions::tile_rows
-constexpr int kWaveThreads = kWaveConsumers + 32;
-constexpr int kWaveStages = 4;
+// One block per sweep (wavefront.h has the schedule and the stream format).  `groups` warp groups of `group_rows`
+// threads take the tiles in turn; one more warp keeps the shared-memory ring filled with bulk copies.  For tile t,
+// thread i of group t % groups
+//   prepares: waits for the tile's bytes, sums the row's OLD entries (values of tiles <= t - groups - 1, complete
+//             since the group's previous tile), fetches the right-hand side and the first fresh entries;
+//   finishes: waits on the named barrier of tile t - 1, adds the FRESH entries from the window, stores the result
+//             into the window, arrives on the barrier of tile t (without waiting), then writes global memory.
+// The hand-off of a level is therefore: barrier release -> shared-memory load -> a few dependent FMAs -> store ->
+// arrive; everything else overlaps with the other groups' tiles.
+constexpr int kWaveBarriers = 8;    // named barriers 1..8, tile t uses 1 + t % 8; a group may wait on tile t + groups - 1's
+                                    // barrier while tile t's is still open, so groups < kWaveBarriers
+constexpr int kWaveMaxThreads = 800;  // 80 registers per thread
+#ifdef S35_WAVE_TRACING
+constexpr bool kWaveTracing = true; // clocks of every tile into WaveArgs::trace (a build for tools/, see Makefile)
+#else
+constexpr bool kWaveTracing = false;
+#endif
+constexpr int kWaveSlots = 32;      // = WavefrontOptions::slots: tiles in flight, one pair of mbarriers each
 
 __device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, int count)
@@ -252,19 +262,25 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
                "r"(parity)
                : "memory");
 }
-// one attempt; its latency overlaps with whatever the thread does until it looks at the answer
-__device__ __forceinline__ uint32_t mbar_try(uint64_t *bar, uint32_t parity)
+// the same by polling: a thread suspended in try_wait was measured to hold up other warps' shared-memory
+// instructions on its scheduler, so the producer (which waits most of the time) polls and sleeps instead
+__device__ __forceinline__ void mbar_wait_polling(uint64_t *bar, uint32_t parity)
 {
-  uint32_t done;
-  asm volatile("{\n"
-               ".reg .pred p;\n"
-               "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-               "selp.u32 %0, 1, 0, p;\n"
-               "}"
-               : "=r"(done)
-               : "r"(smem_addr(bar)), "r"(parity)
-               : "memory");
-  return done;
+  for (;;)
+    {
+      uint32_t done;
+      asm volatile("{\n"
+                   ".reg .pred p;\n"
+                   "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+                   "selp.u32 %0, 1, 0, p;\n"
+                   "}"
+                   : "=r"(done)
+                   : "r"(smem_addr(bar)), "r"(parity)
+                   : "memory");
+      if (done)
+        return;
+      __nanosleep(64);
+    }
 }
 // global -> shared bulk copy (16-byte aligned, a multiple of 16 bytes) that reports to an mbarrier
 __device__ __forceinline__ void bulk_copy_to_shared(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
@@ -279,193 +295,346 @@ __device__ __forceinline__ double ld_l2(const double *p)
   asm volatile("ld.global.cg.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ void group_wait(int tile, int threads)
+{
+  asm volatile("bar.sync %0, %1;" ::"r"(1 + tile % kWaveBarriers), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void group_signal(int tile, int threads)
+{
+  asm volatile("bar.arrive %0, %1;" ::"r"(1 + tile % kWaveBarriers), "r"(threads) : "memory");
+}
 
 struct WaveArgs
 {
-  const int32_t *meta, *directory;
-  const double *values;
-  int32_t n_tiles, window, stage_meta, stage_vals;
+  const unsigned char *blob;
+  const int4 *directory;
+  const int2 *desc;
+  const int32_t *rhs_index;
+  int32_t n_tiles, groups, group_rows, window, ring_bytes;
   const double *rhs;   // right-hand sides, indexed through the plan
-  double *by_position; // the sweep's result in position order (window overflow and the next sweep's input)
-  double *natural;     // the sweep's result by row index, or nullptr
+  double *by_position; // the sweep's result in position order (values that left the window; the next sweep's input)
+  double *natural;     // backward sweep: the result by row index
+  long long *trace;    // S35_WAVE_TRACE: per tile, the clock at four points of its first warp (else nullptr)
 };
 
 template <bool FORWARD>
-__global__ void __launch_bounds__(kWaveThreads, 1) k_wave_sweep(const WaveArgs a)
+__global__ void __launch_bounds__(kWaveMaxThreads, 1) k_wave_sweep(const WaveArgs a)
 {
-  extern __shared__ __align__(16) unsigned char wave_smem[];
+  extern __shared__ __align__(128) unsigned char wave_smem[];
   double *const window = reinterpret_cast<double *>(wave_smem);
-  double *const stage_vals = window + a.window;
-  int32_t *const stage_meta = reinterpret_cast<int32_t *>(stage_vals + (size_t)kWaveStages * a.stage_vals);
-  uint64_t *const full = reinterpret_cast<uint64_t *>(stage_meta + (size_t)kWaveStages * a.stage_meta);
-  uint64_t *const empty = full + kWaveStages;
+  unsigned char *const ring = wave_smem + (size_t)a.window * 8;
+  uint64_t *const full = reinterpret_cast<uint64_t *>(ring + a.ring_bytes);
+  uint64_t *const empty = full + kWaveSlots;
   const int tid = threadIdx.x;
+  const int n_consumers = a.groups * a.group_rows;
   if (tid == 0)
     {
-      for (int s = 0; s < kWaveStages; ++s)
+      for (int s = 0; s < kWaveSlots; ++s)
         {
           mbar_init(full + s, 1);
-          mbar_init(empty + s, 1);
+          mbar_init(empty + s, a.group_rows / 32);
         }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+  for (int k = tid; k < a.window; k += blockDim.x)
+    window[k] = 0.0; // a padding entry multiplies 0.0 with slot 0: it must hold a finite number from the start
   __syncthreads();
 
-  if (tid >= kWaveConsumers)
+  if (tid >= n_consumers)
     {
-      // producer warp: lane 0 keeps the stages filled.  The tile directory is read 32 tiles at a time by the whole
-      // warp, the next batch while the current one is being issued, so that the producer never waits for it.
-      const int lane = tid - kWaveConsumers;
-      const int4 *const directory = reinterpret_cast<const int4 *>(a.directory);
-      int4 next = lane < a.n_tiles ? directory[lane] : make_int4(0, 0, 0, 0);
-      for (int base = 0; base < a.n_tiles; base += 32)
+      // producer: ONE thread issues the copies (no warp-wide instruction may sit between two copies: measured on
+      // B200, a shuffle in this loop waited > 1000 cycles behind the consumers' barrier waits).  The directory is
+      // read eight tiles ahead.
+      if (tid != n_consumers)
+        return;
+      constexpr int kAhead = 8;
+      int4 dir[kAhead];
+#pragma unroll
+      for (int u = 0; u < kAhead; ++u)
+        dir[u] = u < a.n_tiles ? __ldg(a.directory + u) : make_int4(0, 0, 0, 0);
+      int freed = 0; // tiles known to be finished
+      for (int base = 0; base < a.n_tiles; base += kAhead)
         {
-          const int4 batch = next;
-          const int ahead = base + 32 + lane;
-          next = ahead < a.n_tiles ? directory[ahead] : make_int4(0, 0, 0, 0);
-          const int count = min(32, a.n_tiles - base);
-          for (int u = 0; u < count; ++u)
+#pragma unroll
+          for (int u = 0; u < kAhead; ++u)
             {
-              const int32_t meta_off = __shfl_sync(0xffffffffu, batch.x, u), meta_len = __shfl_sync(0xffffffffu, batch.y, u);
-              const int32_t val_off = __shfl_sync(0xffffffffu, batch.z, u), val_len = __shfl_sync(0xffffffffu, batch.w, u);
-              if (lane == 0)
+              const int t = base + u;
+              if (t >= a.n_tiles)
+                break;
+              const int4 d = dir[u];
+              if (t + kAhead < a.n_tiles)
+                dir[u] = __ldg(a.directory + t + kAhead);
+              const int s = t % kWaveSlots;
+              if (kWaveTracing && a.trace)
+                a.trace[24 * (size_t)t + 5] = clock64();
+              while (freed <= d.w)
                 {
-                  const int t = base + u, s = t % kWaveStages;
-                  if (t >= kWaveStages)
-                    mbar_wait(empty + s, (uint32_t)((t / kWaveStages - 1) & 1));
-                  mbar_expect_tx(full + s, (uint32_t)meta_len * 4u + (uint32_t)val_len * 8u);
-                  bulk_copy_to_shared(stage_meta + (size_t)s * a.stage_meta, a.meta + meta_off, (uint32_t)meta_len * 4u, full + s);
-                  if (val_len)
-                    bulk_copy_to_shared(stage_vals + (size_t)s * a.stage_vals, a.values + val_off, (uint32_t)val_len * 8u, full + s);
+                  mbar_wait_polling(empty + freed % kWaveSlots, (uint32_t)((freed / kWaveSlots) & 1));
+                  ++freed;
                 }
-              __syncwarp();
+              if (kWaveTracing && a.trace)
+                a.trace[24 * (size_t)t + 4] = clock64();
+              mbar_expect_tx(full + s, (uint32_t)d.z);
+              bulk_copy_to_shared(ring + (size_t)d.y * 16, a.blob + (size_t)d.x * 16, (uint32_t)d.z, full + s);
             }
         }
       return;
     }
 
-  // consumers
-  double rhs_next = 0.0;
-  if (a.n_tiles > 0)
+  const int group = tid / a.group_rows, i = tid - group * a.group_rows, lane = tid & 31;
+  const int warp_first_row = i - lane;
+  const int pair = 2 * a.group_rows; // threads on a tile's barrier: its own group arrives, the next tile's group waits
+  const uint32_t mask = (uint32_t)a.window - 1u;
+  // Look-ahead without touching the ring, three global loads deep, each issued at the top of one of the group's tiles
+  // and used at the top of the next: a tile's descriptor three tiles ahead, the index of the row's right-hand side
+  // two tiles ahead, the right-hand side itself one tile ahead.
+  auto load_desc = [&](int t) { return t < a.n_tiles ? __ldg(a.desc + t) : make_int2(0, 0); };
+  auto load_index = [&](int2 d) { return i < (d.x & 511) ? __ldg(a.rhs_index + d.y + i) : -1; };
+  auto load_rhs = [&](int32_t index) { return index >= 0 ? ld_l2(a.rhs + index) : 0.0; };
+  int2 desc0 = load_desc(group), desc1 = load_desc(group + a.groups), desc2 = load_desc(group + 2 * a.groups);
+  int32_t index1 = load_index(desc1);
+  double rhs0 = load_rhs(load_index(desc0));
+  for (int t = group; t < a.n_tiles; t += a.groups)
     {
-      mbar_wait(full + 0, 0u);
-      const WaveTile first = wave_tile(stage_meta, stage_vals);
-      if (tid < first.rows)
-        rhs_next = ld_l2(a.rhs + first.rhs[tid]);
-    }
-  for (int t = 0; t < a.n_tiles; ++t)
-    {
-      const int s = t % kWaveStages;
-      // the stage's arrival was awaited when its right-hand sides were fetched
-      const WaveTile tile = wave_tile(stage_meta + (size_t)s * a.stage_meta, stage_vals + (size_t)s * a.stage_vals);
-      const double rhs = rhs_next;
-      // the next tile's stage has normally been complete for a long time: ask now, look at the answer after the row
-      const int s1 = (t + 1) % kWaveStages;
-      const uint32_t parity1 = (uint32_t)(((t + 1) / kWaveStages) & 1);
-      const uint32_t next_landed = t + 1 < a.n_tiles ? mbar_try(full + s1, parity1) : 1u;
-      if (tid < tile.rows)
+      const int32_t desc = desc0.x, desc_first_pos = desc0.y;
+      const double rhs = rhs0;
+      rhs0 = load_rhs(index1);          // for tile t + groups
+      index1 = load_index(desc2);       // for tile t + 2 groups
+      desc0 = desc1;
+      desc1 = desc2;
+      desc2 = load_desc(t + 3 * a.groups);
+      const int rows = desc & 511;
+      const int s = t % kWaveSlots;
+      if (warp_first_row >= rows)
         {
-          const double result =
-            wave_row(tile, tid, rhs, window, WaveFarLoad{a.by_position}, FORWARD);
-          const int32_t pos = tile.first_pos + tid;
-          window[pos & (a.window - 1)] = result;
-          a.by_position[pos] = result;
-          if (a.natural)
-            a.natural[tile.row[tid]] = result;
+          // no row for this warp: it only keeps the barriers' counts right
+          if (t > 0)
+            group_wait(t - 1, pair);
+          if (kWaveTracing && a.trace && lane == 0)
+            a.trace[24 * (size_t)t + 8 + (i >> 5)] = clock64();
+          if (t + 1 < a.n_tiles)
+            group_signal(t, pair);
+          if (kWaveTracing && a.trace && lane == 0)
+            a.trace[24 * (size_t)t + 16 + (i >> 5)] = clock64();
+          if (lane == 0)
+            mbar_arrive(empty + s);
+          continue;
         }
+      const bool tracing = kWaveTracing && a.trace != nullptr && i == 0;
+      if (tracing)
+        a.trace[24 * (size_t)t + 0] = clock64();
+      mbar_wait(full + s, (uint32_t)((t / kWaveSlots) & 1));
+      if (tracing)
+        a.trace[24 * (size_t)t + 1] = clock64();
+      const unsigned char *const tile = ring + (size_t)(desc >> 9) * 128;
+      const int4 head = *reinterpret_cast<const int4 *>(tile); // first position, rows, warps, n_far
+      const uint32_t word = reinterpret_cast<const uint32_t *>(tile)[4 + (i >> 5)];
+      const unsigned char *const block = tile + (size_t)(word >> 16) * 128;
+      const int n_pre = (int)((word >> 8) & 0xffu), n_chunks = (int)(word & 0xffu);
+      const bool active = i < rows;
+      constexpr int kHead = FORWARD ? 0 : kWaveBackwardHead;
+      // this lane's first chunk: slots at +0, values 0-1 at +256, values 2-3 at +768; the next chunk 1280 bytes on
+      const unsigned char *const lane_slots = block + kHead + 8 * lane;
+      const unsigned char *const lane_vals = block + kHead + 256 + 16 * lane;
+      double acc = 0.0, piv = 1.0, result = 0.0;
+      int32_t natural_row = 0;
+      if (!FORWARD)
+        {
+          piv = reinterpret_cast<const double *>(block)[lane];
+          natural_row = reinterpret_cast<const int32_t *>(block + 256)[lane];
+        }
+      // one chunk: four products, the solution values straight from the window (the slots are byte offsets)
+      struct Chunk
+      {
+        uint2 s4;
+        double2 lo, hi;
+      };
+      auto load_chunk = [&](int c) {
+        Chunk k;
+        k.s4 = *reinterpret_cast<const uint2 *>(lane_slots + (size_t)c * kWaveChunkBytes);
+        k.lo = *reinterpret_cast<const double2 *>(lane_vals + (size_t)c * kWaveChunkBytes);
+        k.hi = *reinterpret_cast<const double2 *>(lane_vals + (size_t)c * kWaveChunkBytes + 512);
+        return k;
+      };
+      auto sum_chunk = [&](const Chunk &k, double sum) {
+        const unsigned char *const w = reinterpret_cast<const unsigned char *>(window);
+        const double x0 = *reinterpret_cast<const double *>(w + (k.s4.x & 0xffffu)), x1 = *reinterpret_cast<const double *>(w + (k.s4.x >> 16));
+        const double x2 = *reinterpret_cast<const double *>(w + (k.s4.y & 0xffffu)), x3 = *reinterpret_cast<const double *>(w + (k.s4.y >> 16));
+        sum = fma(k.lo.x, x0, sum);
+        sum = fma(k.lo.y, x1, sum);
+        sum = fma(k.hi.x, x2, sum);
+        return fma(k.hi.y, x3, sum);
+      };
+#pragma unroll 2
+      for (int c = 0; c < n_pre; ++c)
+        acc = sum_chunk(load_chunk(c), acc);
+      if (head.w > 0)
+        {
+          // values that have left the window: a short list per tile, each thread picks its own
+          const WaveFar *const far = reinterpret_cast<const WaveFar *>(tile + 64);
+          for (int f = 0; f < head.w; ++f)
+            if (far[f].row == i)
+              acc = fma(far[f].value, ld_l2(a.by_position + far[f].position), acc);
+        }
+      // the fresh chunks' factor entries are fetched before the wait (the first two; more are rare)
+      const int n_post = n_chunks - n_pre;
+      Chunk post0 = {make_uint2(0u, 0u), make_double2(0., 0.), make_double2(0., 0.)}, post1 = post0;
+      if (n_post > 0)
+        post0 = load_chunk(n_pre);
+      if (n_post > 1)
+        post1 = load_chunk(n_pre + 1);
+      __syncwarp();
+      if (tracing)
+        a.trace[24 * (size_t)t + 2] = clock64();
+      if (t > 0)
+        group_wait(t - 1, pair);
+      if (tracing)
+        a.trace[24 * (size_t)t + 3] = clock64();
+      if (kWaveTracing && a.trace && lane == 0)
+        a.trace[24 * (size_t)t + 8 + (i >> 5)] = clock64();
+      if (n_post > 0)
+        acc = sum_chunk(post0, acc);
+      if (n_post > 1)
+        acc = sum_chunk(post1, acc);
+      for (int c = n_pre + 2; c < n_pre + n_post; ++c)
+        acc = sum_chunk(load_chunk(c), acc);
+      if (active)
+        {
+          result = rhs - acc;
+          if (!FORWARD)
+            result *= piv;
+          window[(uint32_t)(desc_first_pos + i) & mask] = result;
+        }
+      const int32_t first_pos = desc_first_pos;
+      __syncwarp();
       if (t + 1 < a.n_tiles)
+        group_signal(t, pair);
+      if (tracing)
+        a.trace[24 * (size_t)t + 6] = clock64();
+      if (kWaveTracing && a.trace && lane == 0)
+        a.trace[24 * (size_t)t + 16 + (i >> 5)] = clock64();
+      if (lane == 0)
+        mbar_arrive(empty + s); // the tile's bytes are no longer needed by this warp (before the global stores: the
+                                // arrive is a release and would wait for them)
+      if (active)
         {
-          // the next tile's right-hand sides travel while this tile finishes
-          if (!next_landed)
-            mbar_wait(full + s1, parity1);
-          const WaveTile next = wave_tile(stage_meta + (size_t)s1 * a.stage_meta, stage_vals + (size_t)s1 * a.stage_vals);
-          if (tid < next.rows)
-            rhs_next = ld_l2(a.rhs + next.rhs[tid]);
+          a.by_position[first_pos + i] = result;
+          if (!FORWARD)
+            a.natural[natural_row] = result;
         }
-      asm volatile("bar.sync 1, %0;" ::"n"(kWaveConsumers) : "memory"); // window complete for the next tile; stage s read
-      if (tid == 0)
-        mbar_arrive(empty + s);
     }
 }
+#undef S35_WAVE_GATHER
 
-__global__ void k_wave_gather_values(int64_t n, const int32_t *__restrict__ source, const double *__restrict__ lu,
-                                     double *__restrict__ values)
+// stream[dst[i]] = lu[src[i]]: the factor's values into the packed stream after a factorisation
+__global__ void k_wave_fill_values(int64_t n, const int32_t *__restrict__ dst, const int32_t *__restrict__ src,
+                                   const double *__restrict__ lu, double *__restrict__ stream)
 {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
-    values[i] = source[i] >= 0 ? lu[source[i]] : 0.0;
+    stream[dst[i]] = lu[src[i]];
+}
+
+int env_int(const char *name, int fallback)
+{
+  const char *t = std::getenv(name);
+  return t && *t ? std::atoi(t) : fallback;
 }
 
 void wave_launch(DevIlu &p, double *dst, const double *src, cudaStream_t s)
 {
   DevIlu::Wave &w = p.wave;
-  WaveArgs fwd{w.meta[0].ptr, w.directory[0].ptr, w.values[0].ptr, w.n_tiles[0], w.window, w.stage_meta, w.stage_vals,
-               src,           w.by_position[0].ptr, nullptr};
-  WaveArgs bwd{w.meta[1].ptr, w.directory[1].ptr, w.values[1].ptr, w.n_tiles[1], w.window, w.stage_meta, w.stage_vals,
-               w.by_position[0].ptr, w.by_position[1].ptr, dst};
-  S35_LAUNCH((k_wave_sweep<true>), 1, kWaveThreads, w.smem_bytes, s, fwd);
-  S35_LAUNCH((k_wave_sweep<false>), 1, kWaveThreads, w.smem_bytes, s, bwd);
+  WaveArgs fwd{w.blob[0].ptr, reinterpret_cast<const int4 *>(w.directory[0].ptr), reinterpret_cast<const int2 *>(w.desc[0].ptr), w.rhs_index[0].ptr, w.n_tiles[0], w.groups, w.group_rows,
+               w.window, w.ring_bytes, src, w.by_position[0].ptr, nullptr, w.trace.ptr};
+  WaveArgs bwd{w.blob[1].ptr, reinterpret_cast<const int4 *>(w.directory[1].ptr), reinterpret_cast<const int2 *>(w.desc[1].ptr), w.rhs_index[1].ptr, w.n_tiles[1], w.groups, w.group_rows,
+               w.window, w.ring_bytes, w.by_position[0].ptr, w.by_position[1].ptr, dst, nullptr};
+  const int threads = w.groups * w.group_rows + 32;
+  S35_LAUNCH((k_wave_sweep<true>), 1, threads, w.smem_bytes, s, fwd);
+  S35_LAUNCH((k_wave_sweep<false>), 1, threads, w.smem_bytes, s, bwd);
+  if (w.trace.ptr && ++w.trace_calls == 4)
+    {
+      // S35_WAVE_TRACE=<file>: the forward sweep's clocks of the fourth application, one line per tile
+      std::vector<long long> h(w.trace.n);
+      w.trace.download(h.data(), s);
+      if (FILE *f = std::fopen(std::getenv("S35_WAVE_TRACE"), "w"))
+        {
+          for (int t = 0; t < w.n_tiles[0]; ++t)
+            {
+              std::fprintf(f, "%d", t);
+              for (int k = 0; k < 24; ++k)
+                std::fprintf(f, " %lld", h[24 * (size_t)t + k]);
+              std::fprintf(f, "\n");
+            }
+          std::fclose(f);
+        }
+    }
 }
 
 // packs both sweeps of the pattern; returns false if the mode does not suit this factor
 bool wave_create(DevIlu &p, const DevMatrix &A, cudaStream_t s)
 {
   const int32_t n = A.n_rows;
-  if (n == 0 || (double)A.nnz / n > 40.0)
-    return false; // long rows: the wide sweep streams them with many SMs, one SM cannot
+  if (n == 0)
+    return false;
   std::vector<int32_t> diag(n);
   for (int32_t r = 0; r < n; ++r)
     for (int32_t k = A.h_rowptr[r]; k < A.h_rowptr[r + 1]; ++k)
       if (A.h_col[k] == r)
         diag[r] = k;
   WavefrontOptions opt;
-  opt.tile_rows = kWaveConsumers;
-  opt.window = 8192;
-  if (const char *t = std::getenv("S35_WAVE_WINDOW"))
-    opt.window = std::atoi(t);
-  // Tiles as large as the shared memory allows: on the r1 pressure factor 3072 entries per tile give one tile per
-  // level (1 758 tiles for 1 755 levels), 1536 entries split a quarter of the levels (2 402 tiles).
-  std::vector<int> candidates = {3072, 1536, 768};
-  if (const char *t = std::getenv("S35_WAVE_TILE_ENTRIES"))
-    candidates.assign(1, std::atoi(t));
+  opt.groups = env_int("S35_WAVE_GROUPS", opt.groups);
+  opt.group_rows = env_int("S35_WAVE_GROUP_ROWS", opt.group_rows);
+  opt.window = env_int("S35_WAVE_WINDOW", opt.window);
+  opt.ring_bytes = env_int("S35_WAVE_RING_KB", opt.ring_bytes / 1024) * 1024;
+  opt.max_tile_bytes = env_int("S35_WAVE_TILE_KB", opt.max_tile_bytes / 1024) * 1024;
   DevIlu::Wave &w = p.wave;
+  w = DevIlu::Wave();
+  opt.slots = kWaveSlots;
+  w.smem_bytes = (size_t)opt.window * 8 + (size_t)opt.ring_bytes + (size_t)kWaveSlots * 16 + 16;
+  if (opt.groups >= kWaveBarriers || opt.groups * opt.group_rows + 32 > kWaveMaxThreads || w.smem_bytes > 227 * 1024)
+    return false;
   WavefrontPlan F, B;
-  bool fits = false;
-  for (int tile_entries : candidates)
+  try
     {
-      opt.tile_entries = tile_entries;
       F = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), true, nullptr, opt);
       // the backward sweep takes its right-hand sides from the forward sweep's position-ordered result
       B = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), false, F.position.data(), opt);
-      w.window = opt.window;
-      w.stages = kWaveStages;
-      w.stage_meta = round_up(std::max(F.max_meta, B.max_meta), 4);
-      w.stage_vals = round_up(std::max(std::max(F.max_values, B.max_values), 2), 2);
-      w.smem_bytes = (size_t)w.window * 8 + (size_t)kWaveStages * ((size_t)w.stage_vals * 8 + (size_t)w.stage_meta * 4) + 2 * kWaveStages * 8;
-      if (w.smem_bytes <= 227 * 1024)
-        {
-          fits = true;
-          break;
-        }
     }
-  if (!fits)
-    return false;
-  const WavefrontPlan *plans[2] = {&F, &B};
+  catch (const std::invalid_argument &)
+    {
+      return false; // e.g. a row that does not fit a tile: the wide sweep takes this factor
+    }
+  w.groups = opt.groups;
+  w.group_rows = opt.group_rows;
+  w.window = opt.window;
+  w.ring_bytes = opt.ring_bytes;
+  WavefrontPlan *plans[2] = {&F, &B};
   for (int d = 0; d < 2; ++d)
     {
-      const WavefrontPlan &P = *plans[d];
+      WavefrontPlan &P = *plans[d];
       w.n_tiles[d] = P.n_tiles;
-      w.n_values[d] = P.n_values;
+      w.n_levels[d] = P.n_levels;
+      w.n_values[d] = (int64_t)P.value_dst.size();
+      w.stream_bytes[d] = (int64_t)P.blob.size();
       w.far_fraction[d] = P.entries ? (double)P.far_entries / (double)P.entries : 0.0;
-      w.meta[d].upload(P.meta, s);
+      w.fresh_fraction[d] = P.entries ? (double)P.fresh_entries / (double)P.entries : 0.0;
+      w.blob[d].upload(P.blob, s);
       w.directory[d].upload(P.directory, s);
-      std::vector<int32_t> source(P.value_source.begin(), P.value_source.end()); // factor positions fit 32 bits (nnz is int32-indexed)
-      w.value_source[d].upload(source, s);
-      w.values[d].alloc((size_t)std::max<int64_t>(P.n_values, 2));
+      w.desc[d].upload(P.desc, s);
+      w.rhs_index[d].upload(P.rhs_index, s);
+      w.value_dst[d].upload(P.value_dst, s);
+      w.value_src[d].upload(P.value_src, s);
       w.by_position[d].alloc(n);
+      w.by_position[d].zero(s);
     }
-  S35_CUDA(cudaFuncSetAttribute(k_wave_sweep<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w.smem_bytes));
-  S35_CUDA(cudaFuncSetAttribute(k_wave_sweep<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w.smem_bytes));
+  S35_CUDA(cudaFuncSetAttribute(k_wave_sweep<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  S35_CUDA(cudaFuncSetAttribute(k_wave_sweep<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  if (const char *f = std::getenv("S35_WAVE_TRACE"))
+    if (*f && n > 100000) // the large factor of a run only
+      {
+        w.trace.alloc((size_t)24 * w.n_tiles[0]);
+        w.trace.zero(s);
+      }
   w.on = true;
   return true;
 }
@@ -575,10 +744,14 @@ void DevIlu::create(const DevMatrix &A, cudaStream_t s)
   if (const char *g = std::getenv("S35_ILU_BACKOFF_NS"))
     backoff_ns = std::max(0, std::min(10000, std::atoi(g)));
   factored = false;
+  // Which sweep: the wavefront mode (one block, levels handed over inside an SM) wins where the levels are narrow and
+  // the rows short; S35_ILU_MODE = wide | wavefront overrides the choice, S35_WAVE_MAX_ROW moves the row-length bound.
   wave = Wave();
-  if (const char *mode = std::getenv("S35_ILU_MODE"))
-    if (std::strcmp(mode, "wavefront") == 0)
-      wave_create(*this, A, s);
+  const char *mode = std::getenv("S35_ILU_MODE");
+  const bool force_wide = mode && std::strcmp(mode, "wide") == 0, force_wave = mode && std::strcmp(mode, "wavefront") == 0;
+  const double mean_row = n ? (double)A.nnz / n : 0.0;
+  if (!force_wide && (force_wave || mean_row <= (double)env_int("S35_WAVE_MAX_ROW", 40)))
+    wave_create(*this, A, s);
 }
 
 void DevIlu::factor(const double *values, double strengthen_diagonal, cudaStream_t s)
@@ -598,7 +771,8 @@ void DevIlu::factor(const double *values, double strengthen_diagonal, cudaStream
       if (wave.n_values[d])
         {
           const int grid = (int)std::min<int64_t>((wave.n_values[d] + 255) / 256, (int64_t)sm_count() * 8);
-          S35_LAUNCH(k_wave_gather_values, grid, 256, 0, s, wave.n_values[d], wave.value_source[d].ptr, lu.ptr, wave.values[d].ptr);
+          S35_LAUNCH(k_wave_fill_values, grid, 256, 0, s, wave.n_values[d], wave.value_dst[d].ptr, wave.value_src[d].ptr, lu.ptr,
+                     reinterpret_cast<double *>(wave.blob[d].ptr));
         }
   factored = true;
 }

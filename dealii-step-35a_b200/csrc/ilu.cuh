@@ -32,18 +32,21 @@ struct DevIlu
   int backoff_ns = 0;                 // longest pause between polling rounds of a waiting row
   bool factored = false;
 
-  // Wavefront mode (S35_ILU_MODE=wavefront, off by default, for factors with short rows): the sweep runs in ONE
-  // block that walks the dependency levels in order with the recent solution values in shared memory
-  // (wavefront.h).  Index 0: forward sweep, 1: backward sweep.
+  // Wavefront mode (for factors whose dependency levels are narrow): a sweep runs in ONE block that walks the levels
+  // in order with the recent solution values in shared memory (wavefront.h).  Index 0: forward sweep, 1: backward.
   struct Wave
   {
     bool on = false;
-    int32_t n_tiles[2] = {0, 0}, window = 0, stage_meta = 0, stage_vals = 0, stages = 0;
+    int32_t n_tiles[2] = {0, 0}, n_levels[2] = {0, 0};
+    int32_t groups = 0, group_rows = 0, window = 0, ring_bytes = 0;
     size_t smem_bytes = 0;
-    int64_t n_values[2] = {0, 0};
-    DevBuf<int32_t> meta[2], directory[2], value_source[2];
-    DevBuf<double> values[2], by_position[2];
-    double far_fraction[2] = {0., 0.};
+    int64_t n_values[2] = {0, 0}, stream_bytes[2] = {0, 0};
+    DevBuf<unsigned char> blob[2];
+    DevBuf<int32_t> directory[2], desc[2], rhs_index[2], value_dst[2], value_src[2];
+    DevBuf<double> by_position[2];
+    DevBuf<long long> trace; // S35_WAVE_TRACE: clocks of the forward sweep's tiles
+    int trace_calls = 0;
+    double far_fraction[2] = {0., 0.}, fresh_fraction[2] = {0., 0.};
   } wave;
 
   void create(const DevMatrix &A, cudaStream_t s);

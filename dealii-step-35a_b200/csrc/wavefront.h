@@ -1,36 +1,54 @@
-// Level-sequential ("wavefront") schedule of a sparse triangular sweep for ONE thread block, host side: the
-// packed streams the kernel k_wave_sweep (ilu.cu) consumes, and an executor of the same streams on the CPU with
-// which the packing is tested without a GPU (tests/cpp/test_wavefront.cpp).  No CUDA in this file.
+// Level-sequential ("wavefront") schedule of a sparse triangular sweep for ONE thread block, host side: the packed
+// stream the kernel k_wave_sweep (ilu.cu) consumes, and an executor of the same stream on the CPU with which the
+// packing is tested without a GPU (tests/cpp/test_wavefront.cpp).  No CUDA in this file.
 //
-// Why: the substitutions of SparseILU::vmult have thousands of dependency levels of ~100 rows each.  The wide
-// sweep (k_ilu_sweep) pays a round trip through L2 per level.  Here one block walks the levels in order and keeps
-// the most recent `window` solution values in shared memory, so that a level costs shared-memory latency plus a
-// block barrier; the factor arrives through bulk copies that run several tiles ahead.  The arithmetic per row is
-// that of the serial algorithm: the row's entries in ascending column order, one accumulator.
+// Why: the substitutions of SparseILU::vmult have thousands of dependency levels of ~100 rows each.  A sweep that
+// spreads the rows of a level over many SMs pays a trip through L2 per level (measured on B200: ~490 cycles per
+// hand-off, tools/microbench/latency.cu).  Here one block walks the levels in order, keeps the most recent `window`
+// solution values in shared memory, and hands a level over with a named barrier (~110 cycles).
 //
-// Order of the rows ("positions"): by dependency level; inside a level by decreasing number of entries (so that
-// a tile can be stored as jagged diagonals without padding), then by row index.  A TILE is a run of at most
-// tile_rows rows of ONE level with at most tile_entries entries; thread i of the block owns row i of the tile.
+// Order of the rows ("positions"): by dependency level; inside a level by decreasing number of entries, then by row
+// index.  A TILE is a run of at most group_rows rows of ONE level whose packed size is at most max_tile_bytes.  The
+// block has `groups` warp groups of group_rows threads; tile t belongs to group t % groups, lane l of warp w of the
+// group owns row 32 w + l of the tile.
 //
-// Streams (one pair per sweep direction), per tile:
-//   meta (int32, length a multiple of 4):
-//     [0] n_rows  [1] n_entries  [2] max_len  [3] position of the tile's first row
-//     off[max_len rounded up to 4]      entry j of row i sits at  off[j] + i  (jagged diagonal j)
-//     row[n_rows r.u. 4]                natural row index (where the result goes)
-//     rhs[n_rows r.u. 4]                index of the row's right-hand side in the caller's vector
-//     len[n_rows r.u. 4]                number of entries of the row
-//     src[n_entries r.u. 4]             where the solution value of the entry's column is read:
-//                                       >= 0: slot of the shared-memory window;  < 0: ~position, from global memory
-//   values (double, length a multiple of 2):
-//     val[n_entries r.u. 2]             factor entries, same indexing as src
-//     piv[n_rows r.u. 2]                inverse pivots (backward sweep only)
-// A value is "near" (read from the window) if its position is less than `window` behind the END of the reading
-// tile: then no row of that tile overwrites its slot.  Everything else is "far" and read from the position-ordered
-// copy of the solution in global memory, where it has been for a long time.
+// Pipelining: a row's entries are split by the age of the value they read.  OLD entries read values of tiles
+// <= t - groups - 1; those are complete when the group starts on tile t (it has just finished tile t - groups and
+// waited for tile t - groups - 1 then), so they can be summed ahead of time, off the critical path.  FRESH entries
+// (tiles t - groups .. t - 1) are added after the wait for tile t - 1.  Per row the sum runs over the old entries
+// in ascending column order, then over the fresh ones in ascending column order, in one accumulator: a fixed
+// order, so results do not depend on timing; it is a re-association of the serial algorithm's sum.
+//
+// What the format is shaped by (all measured on B200, profiles/ of round 2):
+//  * one SM is bound by instruction issue long before bandwidth: a thread's entries therefore come in CHUNKS of four
+//    (two 16-byte value loads and one 8-byte slot load serve four products), and the chunks of a WARP's 32 rows lie
+//    side by side -- chunk c of the warp is one 1280-byte block (32 x 8 bytes of slots, 32 x 16 of values 0-1, 32 x
+//    16 of values 2-3) -- so that every address is "warp base + lane * size + constant" and the chunk counts are the
+//    same for the whole warp: no per-row index arithmetic, no divergence;
+//  * a bulk copy whose ends are not 128-byte aligned is slow, and only > 100 KB in flight keep the stream going, so
+//    tiles are 128-byte aligned and travel back to back through a byte ring (not through equal stages).
+// Per warp, chunks [0, n_pre) hold the rows' old entries and are summed ahead; chunks [n_pre, n_chunks) hold their
+// fresh entries; rows with fewer entries than the warp's counts are padded (value 0.0, slot 0; the window starts as
+// zeros, so a padding product is 0 * finite).
+// The few old entries whose value has left the window ("far": its position is more than `window` behind the END
+// of the reading tile, so a concurrently running row may overwrite its slot) are kept out of the chunks, in a list
+// per tile that the owning thread walks ahead of time.
+//
+// Packed tile (byte offsets from the tile's start; tile start and size are multiples of 128):
+//   header   16 x int32   [0] first position  [1] rows  [2] warps  [3] n_far
+//                         [4 + w] warp w: (block offset / 128) << 16 | n_pre << 8 | n_chunks
+//   far      n_far x 16 bytes   int32 row in tile, int32 position, double value
+//   warp block (128-byte aligned), for each warp:
+//       backward sweep only: 32 doubles inverse pivots, 32 int32 natural row indices
+//       n_chunks x { 32 x 4 uint16 slots (byte offsets into the window) | 32 x 2 doubles | 32 x 2 doubles }
+// Beside the stream there are two small arrays the warps look ahead with, without touching the ring:
+//   desc[t] = { rows | (ring offset / 128) << 9, position of the tile's first row }
+//   rhs_index[position] = index of the row's right-hand side in the vector the sweep reads
 #pragma once
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstring>
 #include <stdexcept>
 #include <vector>
 
@@ -38,112 +56,42 @@ namespace s35 {
 
 struct WavefrontOptions
 {
-  int tile_rows = 256;     // = consumer threads of the block
-  int tile_entries = 1536; // bound on a tile's entries (stage size in shared memory)
-  int window = 16384;      // solution values kept in shared memory; a power of two
+  int group_rows = 256;           // threads of a warp group = most rows of a tile; a multiple of 32, at most 256
+  int groups = 3;                 // warp groups (>= 2)
+  int window = 8192;              // solution values kept in shared memory; a power of two, <= 8192 (16-bit byte offsets)
+  int ring_bytes = 144 * 1024;    // shared-memory ring the tiles travel through; a multiple of 128, <= 256 KB
+  int max_tile_bytes = 48 * 1024; // bound on a packed tile (several tiles must fit the ring)
+  int slots = 32;                 // tiles in flight at most (one pair of mbarriers each)
 };
 
 struct WavefrontPlan
 {
   int32_t n = 0;
   bool forward = true;
-  int32_t window = 0;
+  WavefrontOptions opt;
   int32_t n_tiles = 0, n_levels = 0;
-  std::vector<int32_t> meta;       // all tiles' meta blocks
-  std::vector<int32_t> directory;  // per tile: meta offset (ints), meta length (ints), value offset (doubles), value length
-  std::vector<int64_t> value_source; // per slot of the value stream: index into the factor's value array, -1 = 0.0
-  std::vector<int32_t> position;   // position of every row in this sweep's order
-  int64_t n_values = 0;            // length of the value stream
-  int32_t max_meta = 0, max_values = 0; // largest tile (ints / doubles): the stage size
-  int64_t entries = 0, far_entries = 0;
+  std::vector<unsigned char> blob;   // all tiles back to back
+  std::vector<int32_t> directory;    // per tile: blob offset / 16, ring offset / 16, bytes, tile that must be finished before
+                                     // this one may be loaded over it (-1: none)
+  std::vector<int32_t> desc;         // per tile: rows | (ring offset / 128) << 9, first position
+  std::vector<int32_t> rhs_index;    // per position: where the row's right-hand side is read
+  std::vector<int32_t> value_dst;    // blob offset / 8 of every factor value in the stream ...
+  std::vector<int32_t> value_src;    // ... and its index in the factor's value array
+  std::vector<int32_t> position;     // position of every row in this sweep's order
+  int64_t entries = 0, far_entries = 0, fresh_entries = 0, stored_entries = 0, post_chunks = 0, warp_tiles = 0;
+  int32_t max_tile = 0, max_post_chunks = 0; // largest tile in bytes; most chunks a warp sums after the wait
 };
 
 inline int32_t round_up(int32_t x, int32_t m) { return (x + m - 1) / m * m; }
 
-#if defined(__CUDACC__)
-#define S35_WAVE_INLINE __host__ __device__ __forceinline__
-#else
-#define S35_WAVE_INLINE inline
-#endif
+constexpr int32_t kWaveChunkBytes = 1280;      // one chunk of one warp
+constexpr int32_t kWaveBackwardHead = 384;     // pivots and natural row indices of one warp (backward sweep)
 
-// A tile as it lies in the two streams (or in a stage of shared memory).  The kernel and the CPU walk below use
-// these two functions, so the index arithmetic and the order of the operations of the kernel are what the CPU
-// test exercises.
-struct WaveTile
+struct WaveFar
 {
-  int32_t rows, entries, max_len, first_pos;
-  const int32_t *off, *row, *rhs, *len, *src;
-  const double *val, *piv;
+  int32_t row, position;
+  double value;
 };
-
-S35_WAVE_INLINE WaveTile wave_tile(const int32_t *m, const double *v)
-{
-  WaveTile t;
-  t.rows = m[0];
-  t.entries = m[1];
-  t.max_len = m[2];
-  t.first_pos = m[3];
-  const int32_t rows_pad = (t.rows + 3) & ~3;
-  t.off = m + 4;
-  t.row = t.off + ((t.max_len + 3) & ~3);
-  t.rhs = t.row + rows_pad;
-  t.len = t.rhs + rows_pad;
-  t.src = t.len + rows_pad;
-  t.val = v;
-  t.piv = v + ((t.entries + 1) & ~1);
-  return t;
-}
-
-// reads a solution value that has left the window from the position-ordered array; on the device through L2
-// (the value was stored by another thread of the block, long ago)
-struct WaveFarLoad
-{
-  const double *by_position;
-  S35_WAVE_INLINE double operator()(int32_t pos) const
-  {
-#if defined(__CUDA_ARCH__)
-    double v;
-    asm volatile("ld.global.cg.f64 %0, [%1];" : "=d"(v) : "l"(by_position + pos) : "memory");
-    return v;
-#else
-    return by_position[pos];
-#endif
-  }
-};
-
-// Row i of the tile: rhs - sum_j val_j * solution(column_j), times the inverse pivot in the backward sweep.  Eight
-// entries at a time, all their loads issued before the first product is needed; the products are added in
-// ascending column order into one accumulator.  far(position) reads a value that has left the window.
-S35_WAVE_INLINE double wave_row(const WaveTile &t, int32_t i, double rhs, const double *window, WaveFarLoad far, bool forward)
-{
-  const int32_t n_mine = t.len[i];
-  double acc = 0.0;
-  for (int32_t j0 = 0; j0 < n_mine; j0 += 8)
-    {
-      int32_t where[8];
-      double factor[8], solved[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u)
-        if (j0 + u < n_mine)
-          {
-            const int32_t e = t.off[j0 + u] + i;
-            where[u] = t.src[e];
-            factor[u] = t.val[e];
-          }
-#pragma unroll
-      for (int u = 0; u < 8; ++u)
-        if (j0 + u < n_mine)
-          solved[u] = where[u] >= 0 ? window[where[u]] : far(~where[u]);
-#pragma unroll
-      for (int u = 0; u < 8; ++u)
-        if (j0 + u < n_mine)
-          acc = fma(factor[u], solved[u], acc);
-    }
-  double result = rhs - acc;
-  if (!forward)
-    result *= t.piv[i];
-  return result;
-}
 
 // rowptr/col: CSR with ascending columns; diag[r]: position of the diagonal entry of row r.
 // forward: the strictly lower part (unit diagonal); backward: the strictly upper part and the pivot at diag[r].
@@ -151,18 +99,22 @@ S35_WAVE_INLINE double wave_row(const WaveTile &t, int32_t i, double rhs, const 
 inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int32_t *col, const int32_t *diag, bool forward,
                                     const int32_t *rhs_index, const WavefrontOptions &opt)
 {
-  if (opt.window <= 0 || (opt.window & (opt.window - 1)) != 0)
-    throw std::invalid_argument("wavefront: the window must be a power of two");
-  if (opt.tile_rows <= 0 || opt.tile_entries <= 0)
-    throw std::invalid_argument("wavefront: bad tile bounds");
-  if (opt.tile_rows > opt.window)
-    throw std::invalid_argument("wavefront: a tile must not have more rows than the window has slots"); // two rows, one slot
+  if (opt.window <= 0 || (opt.window & (opt.window - 1)) != 0 || opt.window > 8192)
+    throw std::invalid_argument("wavefront: the window must be a power of two, at most 8192");
+  if (opt.group_rows <= 0 || opt.group_rows % 32 != 0 || opt.group_rows > 256 || opt.groups < 2)
+    throw std::invalid_argument("wavefront: a warp group is a multiple of 32 threads (at most 256), and there are at least two groups");
+  if ((int64_t)opt.group_rows * (opt.groups + 1) > opt.window)
+    throw std::invalid_argument("wavefront: the window must hold the rows of groups + 1 tiles"); // fresh values are near
+  if (opt.ring_bytes % 128 != 0 || opt.ring_bytes > 256 * 1024 || opt.max_tile_bytes > opt.ring_bytes / 2 || opt.slots < opt.groups + 1)
+    throw std::invalid_argument("wavefront: bad ring / tile / slot sizes");
   WavefrontPlan P;
   P.n = n;
   P.forward = forward;
-  P.window = opt.window;
+  P.opt = opt;
   auto first = [&](int32_t r) { return forward ? rowptr[r] : diag[r] + 1; };
   auto last = [&](int32_t r) { return forward ? diag[r] : rowptr[r + 1]; };
+  auto len_of = [&](int32_t r) { return last(r) - first(r); };
+  const int32_t warp_head = forward ? 0 : kWaveBackwardHead;
 
   // dependency levels
   std::vector<int32_t> level(n, 0);
@@ -185,7 +137,7 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
   std::sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
     if (level[a] != level[b])
       return level[a] < level[b];
-    const int32_t la = last(a) - first(a), lb = last(b) - first(b);
+    const int32_t la = len_of(a), lb = len_of(b);
     if (la != lb)
       return la > lb;
     return a < b;
@@ -194,117 +146,304 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
   for (int32_t p = 0; p < n; ++p)
     P.position[order[p]] = p;
 
-  // tiles
-  int32_t p = 0;
-  while (p < n)
-    {
-      const int32_t lv = level[order[p]];
-      int32_t rows = 0, entries = 0;
-      while (p + rows < n && level[order[p + rows]] == lv && rows < opt.tile_rows)
-        {
-          const int32_t r = order[p + rows];
-          const int32_t len = last(r) - first(r);
-          if (len > opt.tile_entries)
-            throw std::invalid_argument("wavefront: a row has more entries than a tile may hold");
-          if (rows > 0 && entries + len > opt.tile_entries)
-            break;
-          entries += len;
-          ++rows;
-        }
-      const int32_t tile_end = p + rows;
-      const int32_t max_len = last(order[p]) - first(order[p]); // rows are sorted by decreasing length
-      const int32_t off_pad = round_up(max_len, 4), rows_pad4 = round_up(rows, 4), ent_pad4 = round_up(entries, 4);
-      const int32_t ent_pad2 = round_up(entries, 2), rows_pad2 = forward ? 0 : round_up(rows, 2);
-      const int64_t meta_begin = (int64_t)P.meta.size(), val_begin = P.n_values;
-      const int32_t meta_len = 4 + off_pad + 3 * rows_pad4 + ent_pad4, val_len = ent_pad2 + rows_pad2;
-      if (meta_begin + meta_len > INT32_MAX || val_begin + val_len > INT32_MAX)
-        throw std::invalid_argument("wavefront: streams exceed 32-bit offsets");
-      P.meta.resize(meta_begin + meta_len, 0);
-      P.value_source.resize(val_begin + val_len, -1);
-      int32_t *m = P.meta.data() + meta_begin;
-      m[0] = rows;
-      m[1] = entries;
-      m[2] = max_len;
-      m[3] = p;
-      int32_t *off = m + 4, *row = off + off_pad, *rhs = row + rows_pad4, *len = rhs + rows_pad4, *src = len + rows_pad4;
-      // jagged diagonals: cnt[j] rows have more than j entries; they are the first cnt[j] rows of the tile
+  // tile boundaries first (an entry is old or fresh by the TILE of the value it reads); the size bound assumes the
+  // worst: every entry in a chunk of its own warp's longest row, plus a far record
+  std::vector<int32_t> tile_begin; // positions; one more entry at the end
+  {
+    int32_t p = 0;
+    while (p < n)
       {
-        int32_t running = 0;
-        for (int32_t j = 0; j < max_len; ++j)
+        const int32_t lv = level[order[p]];
+        int32_t rows = 0, bytes = 64;
+        while (p + rows < n && level[order[p + rows]] == lv && rows < opt.group_rows)
           {
-            off[j] = running;
-            int32_t cnt = 0;
-            while (cnt < rows && last(order[p + cnt]) - first(order[p + cnt]) > j)
-              ++cnt;
-            running += cnt;
+            const int32_t r = order[p + rows];
+            int32_t add = 0;
+            for (int32_t k = first(r); k < last(r); ++k) // far records, at most (the tile ends at p + group_rows at the latest)
+              add += P.position[col[k]] < p + opt.group_rows - opt.window ? 16 : 0;
+            if (rows % 32 == 0)           // a new warp: its longest row comes first
+              add += 128 + warp_head + kWaveChunkBytes * ((len_of(r) + 3) / 4 + 1);
+            if (round_up(bytes + add, 128) > opt.max_tile_bytes)
+              {
+                if (rows == 0)
+                  throw std::invalid_argument("wavefront: a row does not fit a tile");
+                break;
+              }
+            bytes += add;
+            ++rows;
           }
-        if (running != entries)
-          throw std::logic_error("wavefront: jagged diagonal sizes do not add up");
+        tile_begin.push_back(p);
+        p += rows;
       }
+    tile_begin.push_back(n);
+  }
+  P.n_tiles = (int32_t)tile_begin.size() - 1;
+  P.rhs_index.assign(n, 0);
+  std::vector<int32_t> tile_of(n);
+  for (int32_t t = 0; t < P.n_tiles; ++t)
+    for (int32_t p = tile_begin[t]; p < tile_begin[t + 1]; ++p)
+      tile_of[p] = t;
+
+  int32_t ring_cursor = 0;
+  std::vector<int32_t> ring_begin(P.n_tiles), ring_end(P.n_tiles);
+  int32_t oldest_live = 0; // tiles before this one have been overwritten in the ring by earlier decisions
+  struct Entry
+  {
+    int32_t k, slot; // factor position; byte offset in the window
+  };
+  std::vector<std::vector<Entry>> near(opt.group_rows); // per row of the tile: old entries first, far ones left out
+  std::vector<int32_t> n_old(opt.group_rows);
+  std::vector<WaveFar> far;
+  std::vector<int32_t> far_k;
+  for (int32_t t = 0; t < P.n_tiles; ++t)
+    {
+      const int32_t p = tile_begin[t], tile_end = tile_begin[t + 1], rows = tile_end - p, warps = (rows + 31) / 32;
+      far.clear();
+      far_k.clear();
       for (int32_t i = 0; i < rows; ++i)
         {
           const int32_t r = order[p + i];
-          row[i] = r;
-          rhs[i] = rhs_index ? rhs_index[r] : r;
-          len[i] = last(r) - first(r);
-          for (int32_t j = 0; j < len[i]; ++j)
+          P.rhs_index[p + i] = rhs_index ? rhs_index[r] : r;
+          near[i].clear();
+          for (int pass = 0; pass < 2; ++pass) // old entries, then fresh ones; ascending columns in both
             {
-              const int32_t k = first(r) + j, q = P.position[col[k]];
-              if (q < 0 || q >= p)
-                throw std::logic_error("wavefront: a dependency is not in an earlier tile");
-              const int32_t e = off[j] + i;
-              const bool near = q >= tile_end - opt.window;
-              src[e] = near ? (q & (opt.window - 1)) : ~q;
-              P.far_entries += near ? 0 : 1;
-              P.value_source[val_begin + e] = k;
+              for (int32_t k = first(r); k < last(r); ++k)
+                {
+                  const int32_t q = P.position[col[k]];
+                  if (q < 0 || q >= p)
+                    throw std::logic_error("wavefront: a dependency is not in an earlier tile");
+                  const bool old = tile_of[q] <= t - opt.groups - 1;
+                  if (old != (pass == 0))
+                    continue;
+                  if (q < tile_end - opt.window)
+                    {
+                      if (!old)
+                        throw std::logic_error("wavefront: a fresh value outside the window");
+                      far.push_back(WaveFar{i, q, 0.0});
+                      far_k.push_back(k);
+                    }
+                  else
+                    near[i].push_back(Entry{k, 8 * (q & (opt.window - 1))});
+                }
+              if (pass == 0)
+                n_old[i] = (int32_t)near[i].size();
             }
-          if (!forward)
-            P.value_source[val_begin + ent_pad2 + i] = diag[r];
+          P.entries += len_of(r);
+          P.fresh_entries += (int64_t)near[i].size() - n_old[i];
         }
-      P.entries += entries;
-      P.directory.push_back((int32_t)meta_begin);
-      P.directory.push_back(meta_len);
-      P.directory.push_back((int32_t)val_begin);
-      P.directory.push_back(val_len);
-      P.n_values += val_len;
-      P.max_meta = std::max(P.max_meta, meta_len);
-      P.max_values = std::max(P.max_values, val_len);
-      ++P.n_tiles;
-      p = tile_end;
+      P.far_entries += (int64_t)far.size();
+      // warp blocks
+      int32_t cursor = round_up(64 + 16 * (int32_t)far.size(), 128);
+      int32_t warp_word[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      int32_t warp_at[8];
+      for (int32_t w = 0; w < warps; ++w)
+        {
+          // old entries fill the warp's first n_pre chunks, fresh ones the n_post chunks after them (each row padded
+          // with zeros to the warp's counts): after the wait a warp sums fresh entries only
+          int32_t n_pre = 0, n_post = 0;
+          const int32_t lanes = std::min(32, rows - 32 * w);
+          for (int32_t l = 0; l < lanes; ++l)
+            {
+              n_pre = std::max(n_pre, (n_old[32 * w + l] + 3) / 4);
+              n_post = std::max(n_post, ((int32_t)near[32 * w + l].size() - n_old[32 * w + l] + 3) / 4);
+            }
+          if (n_pre + n_post > 255)
+            throw std::invalid_argument("wavefront: a row has more than 255 chunks");
+          warp_at[w] = cursor;
+          warp_word[w] = ((cursor / 128) << 16) | (n_pre << 8) | (n_pre + n_post);
+          cursor = round_up(cursor + warp_head + kWaveChunkBytes * (n_pre + n_post), 128);
+          P.post_chunks += n_post;
+          P.max_post_chunks = std::max(P.max_post_chunks, n_post);
+          P.stored_entries += (int64_t)128 * (n_pre + n_post);
+          ++P.warp_tiles;
+        }
+      const int32_t bytes = round_up(cursor, 128);
+      if (bytes > opt.max_tile_bytes)
+        throw std::logic_error("wavefront: tile larger than planned");
+      const int64_t blob_begin = (int64_t)P.blob.size();
+      if (blob_begin + bytes > (int64_t)INT32_MAX * 8)
+        throw std::invalid_argument("wavefront: stream exceeds 32-bit offsets");
+      P.blob.resize(blob_begin + bytes, 0);
+      unsigned char *base = P.blob.data() + blob_begin;
+      int32_t *h = reinterpret_cast<int32_t *>(base);
+      h[0] = p;
+      h[1] = rows;
+      h[2] = warps;
+      h[3] = (int32_t)far.size();
+      for (int32_t w = 0; w < 8; ++w)
+        h[4 + w] = warp_word[w];
+      for (size_t f = 0; f < far.size(); ++f)
+        {
+          std::memcpy(base + 64 + 16 * f, &far[f], 16);
+          P.value_dst.push_back((int32_t)((blob_begin + 64 + 16 * (int64_t)f + 8) / 8));
+          P.value_src.push_back(far_k[f]);
+        }
+      for (int32_t w = 0; w < warps; ++w)
+        {
+          unsigned char *wb = base + warp_at[w];
+          const int32_t lanes = std::min(32, rows - 32 * w);
+          for (int32_t l = 0; l < lanes; ++l)
+            {
+              const int32_t i = 32 * w + l, r = order[p + i];
+              if (!forward)
+                {
+                  reinterpret_cast<int32_t *>(wb + 256)[l] = r;
+                  P.value_dst.push_back((int32_t)((blob_begin + warp_at[w] + 8 * l) / 8));
+                  P.value_src.push_back(diag[r]);
+                }
+              const int32_t n_pre = (warp_word[w] >> 8) & 0xff;
+              for (size_t j = 0; j < near[i].size(); ++j)
+                {
+                  // old entry j sits at place j, fresh entry j at place 4 n_pre + (j - n_old)
+                  const int32_t place = (int32_t)j < n_old[i] ? (int32_t)j : 4 * n_pre + (int32_t)j - n_old[i];
+                  const int32_t c = place / 4, u = place % 4;
+                  unsigned char *cb = wb + warp_head + kWaveChunkBytes * c;
+                  reinterpret_cast<uint16_t *>(cb)[4 * l + u] = (uint16_t)near[i][j].slot;
+                  const int32_t o_val = warp_at[w] + warp_head + kWaveChunkBytes * c + (u < 2 ? 256 : 768) + 16 * l + 8 * (u & 1);
+                  P.value_dst.push_back((int32_t)((blob_begin + o_val) / 8));
+                  P.value_src.push_back(near[i][j].k);
+                }
+            }
+        }
+      P.max_tile = std::max(P.max_tile, bytes);
+
+      // place in the ring; the tiles it overwrites must be finished before it may be loaded
+      if (ring_cursor + bytes > opt.ring_bytes)
+        ring_cursor = 0;
+      ring_begin[t] = ring_cursor;
+      ring_end[t] = ring_cursor + bytes;
+      ring_cursor += bytes;
+      int32_t need = -1;
+      for (int32_t u = oldest_live; u < t; ++u)
+        if (ring_begin[u] < ring_end[t] && ring_begin[t] < ring_end[u])
+          need = u;
+      if (need >= 0)
+        oldest_live = need + 1;
+      need = std::max(need, t - opt.slots); // and its pair of barriers must be free
+      P.directory.push_back((int32_t)(blob_begin / 16));
+      P.directory.push_back(ring_begin[t] / 16);
+      P.directory.push_back(bytes);
+      P.directory.push_back(need);
+      P.desc.push_back(rows | ((ring_begin[t] / 128) << 9));
+      P.desc.push_back(p);
     }
   return P;
 }
 
-// value stream of a plan from the factor's value array
-inline std::vector<double> wavefront_values(const WavefrontPlan &P, const double *lu)
+// writes the factor's values into the stream
+inline void wavefront_fill_values(WavefrontPlan &P, const double *lu)
 {
-  std::vector<double> v(P.n_values, 0.0);
-  for (int64_t s = 0; s < P.n_values; ++s)
-    if (P.value_source[s] >= 0)
-      v[s] = lu[P.value_source[s]];
-  return v;
+  double *slots = reinterpret_cast<double *>(P.blob.data());
+  for (size_t s = 0; s < P.value_dst.size(); ++s)
+    slots[P.value_dst[s]] = lu[P.value_src[s]];
 }
 
-// The kernel's walk over the streams, on the CPU.  rhs: the vector the rows' right-hand sides are read from
-// (through the rhs index of the plan); by_position: the solution in position order (also the source of far
-// values); natural: the solution by row index, or nullptr.  The rows of a tile are visited last to first and
-// write the window at once, so a window slot that a tile overwrites while it still needs it shows up as a
-// wrong result.
-inline void wavefront_apply_host(const WavefrontPlan &P, const double *values, const double *rhs, double *by_position, double *natural)
+// The kernel's walk over the stream, on the CPU, with the kernel's timing made adversarial: a tile is copied into
+// the ring (a real buffer of ring_bytes) as EARLY as the directory allows, the part of tile u that is summed ahead
+// is summed as early as the kernel may do it -- when only tiles <= u - groups - 1 are finished; every window slot
+// written by a younger tile is poisoned (NaN) for the duration -- and a tile must not read its own slots.  A wrong
+// `need`, a window slot overwritten too early or an entry classified old too early shows up as a wrong result.
+// by_position should come in as NaN.
+inline void wavefront_apply_host(const WavefrontPlan &P, const double *rhs, double *by_position, double *natural)
 {
-  std::vector<double> window(P.window, 0.0);
+  const WavefrontOptions &o = P.opt;
+  const int32_t warp_head = P.forward ? 0 : kWaveBackwardHead;
+  std::vector<double> window(o.window, 0.0);
+  std::vector<unsigned char> ring(o.ring_bytes, 0xA5);
+  const int G = o.groups;
+  std::vector<double> acc_old((size_t)(G + 1) * o.group_rows);
+  std::vector<int32_t> first_pos(P.n_tiles + 1, P.n);
+  for (int32_t t = 0; t < P.n_tiles; ++t)
+    first_pos[t] = P.desc[2 * (size_t)t + 1];
+  int32_t next_load = 0, next_prepare = 0;
+  auto tile_at = [&](int32_t t) { return ring.data() + (size_t)(P.desc[2 * (size_t)t] >> 9) * 128; };
+  // chunks [c0, c1) of lane l of a warp block added to acc
+  auto chunks = [&](const unsigned char *wb, int32_t l, int32_t c0, int32_t c1, double acc, const std::vector<double> &win) {
+    for (int32_t c = c0; c < c1; ++c)
+      {
+        const unsigned char *cb = wb + warp_head + kWaveChunkBytes * c;
+        for (int u = 0; u < 4; ++u)
+          {
+            const uint32_t off = reinterpret_cast<const uint16_t *>(cb)[4 * l + u];
+            const double v = reinterpret_cast<const double *>(cb + (u < 2 ? 256 : 768))[2 * l + (u & 1)];
+            if (v != 0.0) // a padding entry (0.0 * slot 0) contributes nothing; the kernel's window holds no NaN to spoil it
+              acc = std::fma(v, win[off / 8], acc);
+          }
+      }
+    return acc;
+  };
+  auto progress = [&](int32_t finished) { // tiles < finished are complete
+    while (next_load < P.n_tiles && P.directory[4 * (size_t)next_load + 3] < finished)
+      {
+        const int32_t *d = P.directory.data() + 4 * (size_t)next_load;
+        if (d[1] * 16 != (P.desc[2 * (size_t)next_load] >> 9) * 128)
+          throw std::logic_error("wavefront: directory and descriptor disagree");
+        std::memcpy(ring.data() + (size_t)d[1] * 16, P.blob.data() + (size_t)d[0] * 16, d[2]);
+        ++next_load;
+      }
+    while (next_prepare < next_load && next_prepare <= finished + G)
+      {
+        const int32_t u = next_prepare;
+        // what the kernel may rely on: tiles <= u - G - 1.  Poison everything younger that is already in the window.
+        std::vector<double> poisoned = window;
+        for (int32_t q = first_pos[std::max(0, u - G)]; q < first_pos[finished]; ++q)
+          poisoned[q & (o.window - 1)] = std::nan("");
+        const unsigned char *T = tile_at(u);
+        const int32_t *h = reinterpret_cast<const int32_t *>(T);
+        const int32_t rows = h[1], n_far = h[3];
+        if (rows != (P.desc[2 * (size_t)u] & 511) || h[0] != first_pos[u])
+          throw std::logic_error("wavefront: descriptor and tile header disagree");
+        for (int32_t i = 0; i < rows; ++i)
+          {
+            const int32_t word = h[4 + i / 32];
+            const unsigned char *wb = T + (size_t)((uint32_t)word >> 16) * 128;
+            double acc = chunks(wb, i % 32, 0, (word >> 8) & 0xff, 0.0, poisoned);
+            for (int32_t f = 0; f < n_far; ++f)
+              {
+                WaveFar e;
+                std::memcpy(&e, T + 64 + 16 * (size_t)f, 16);
+                if (e.row == i)
+                  acc = std::fma(e.value, by_position[e.position], acc);
+              }
+            acc_old[(size_t)(u % (G + 1)) * o.group_rows + i] = acc;
+          }
+        ++next_prepare;
+      }
+  };
+  progress(0);
   for (int32_t t = 0; t < P.n_tiles; ++t)
     {
-      const WaveTile tile = wave_tile(P.meta.data() + P.directory[4 * t], values + P.directory[4 * t + 2]);
-      for (int32_t i = tile.rows - 1; i >= 0; --i)
+      if (next_prepare <= t)
+        throw std::logic_error("wavefront: the schedule is stuck (a tile waits for ring space held by a later one)");
+      const unsigned char *T = tile_at(t);
+      const int32_t *h = reinterpret_cast<const int32_t *>(T);
+      const int32_t rows = h[1];
+      // a value of this tile's own slots must not be read by the tile: poison them first
+      std::vector<double> win = window;
+      for (int32_t i = 0; i < rows; ++i)
+        win[(h[0] + i) & (o.window - 1)] = std::nan("");
+      std::vector<double> res(rows);
+      for (int32_t i = 0; i < rows; ++i)
         {
-          const double res = wave_row(tile, i, rhs[tile.rhs[i]], window.data(), WaveFarLoad{by_position}, P.forward);
-          const int32_t pos = tile.first_pos + i;
-          window[pos & (P.window - 1)] = res;
-          by_position[pos] = res;
-          if (natural)
-            natural[tile.row[i]] = res;
+          const int32_t word = h[4 + i / 32];
+          const unsigned char *wb = T + (size_t)((uint32_t)word >> 16) * 128;
+          const double acc = chunks(wb, i % 32, (word >> 8) & 0xff, word & 0xff, acc_old[(size_t)(t % (G + 1)) * o.group_rows + i], win);
+          res[i] = rhs[P.rhs_index[h[0] + i]] - acc;
+          if (!P.forward)
+            res[i] *= reinterpret_cast<const double *>(wb)[i % 32];
         }
+      for (int32_t i = 0; i < rows; ++i)
+        {
+          const int32_t pos = h[0] + i;
+          window[pos & (o.window - 1)] = res[i];
+          by_position[pos] = res[i];
+          if (natural && !P.forward)
+            {
+              const unsigned char *wb = T + (size_t)((uint32_t)h[4 + i / 32] >> 16) * 128;
+              natural[reinterpret_cast<const int32_t *>(wb + 256)[i % 32]] = res[i];
+            }
+        }
+      progress(t + 1);
     }
 }
 

@@ -15,6 +15,9 @@ disc = pkg.Disc(os.path.join(ROOT, "meshes", mesh + ".s35m"), dim, params)
 ctx = pkg.Ctx(disc.problem)
 ctx.set_field(pkg.PRES_N, disc.initial_pressure)
 ctx.set_field(pkg.PRES_N_MINUS_1, disc.initial_pressure)
-ctx.advance(2, 1)
+try:
+    ctx.advance(2, 1)  # factorises; under a timing experiment that breaks the sweeps the solvers give up, which is fine here
+except pkg.S35Error as err:
+    print("advance:", str(err)[:100])
 ms, nbytes, launches = ctx.bench_kernel(which, warmup=2, reps=3, flush_l2=False)
 print("ms per apply", ms)
