@@ -104,12 +104,16 @@ k_spmv_rows(int32_t n_rows, const int32_t *__restrict__ rowptr, const int32_t *_
     y[row0 + lane] = add ? y[row0 + lane] + mine : mine;
 }
 
-// rows in flight per warp for matrices whose rows take a whole warp (0: the plain row-per-warp kernel)
+// rows in flight per warp for matrices whose rows take a whole warp (0: the plain row-per-warp kernel; S35_SPMV_ROWS
+// overrides, tools/tune_spmv.py compares)
 int rows_in_flight()
 {
   if (const char *t = std::getenv("S35_SPMV_ROWS"))
     return std::atoi(t);
-  return 0;
+  // measured on B200 (velocity matrix, r1, L2 flushed): 0.350 ms plain, 0.303 / 0.283 / 0.311 ms with 2 / 4 / 8 rows in
+  // flight.  A CSR-stream kernel (products staged in shared memory, block nonzero ranges cut on the host) was tried in
+  // round 2 and reached 0.302 ms on this matrix and lost on the others: not kept.
+  return 4;
 }
 
 template <int R>

@@ -7,8 +7,8 @@
 // hand-off, tools/microbench/latency.cu).  Here one block walks the levels in order, keeps the most recent `window`
 // solution values in shared memory, and hands a level over with a named barrier (~110 cycles).
 //
-// Order of the rows ("positions"): by dependency level; inside a level by decreasing number of entries, then by row
-// index.  A TILE is a run of at most group_rows rows of ONE level whose packed size is at most max_tile_bytes.  The
+// Order of the rows ("positions"): by dependency level; inside a level by decreasing numbers of entry chunks, then by
+// row index.  A TILE is a run of at most group_rows rows of ONE level whose packed size is at most max_tile_bytes.  The
 // block has `groups` warp groups of group_rows threads; tile t belongs to group t % groups, lane l of warp w of the
 // group owns row 32 w + l of the tile.
 //
@@ -130,16 +130,45 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
     }
   P.n_levels = n_levels;
 
-  // rows by (level, more entries first, row index)
+  // Rows by (level, chunks of old entries, chunks of fresh entries, row index), larger first: a warp's 32 rows are
+  // padded to the warp's largest counts, so rows with equal counts should sit together.  Old and fresh are not known
+  // exactly before the tiles are cut; here an entry counts as fresh if its value is produced less than
+  // (groups + 1) * group_rows / 2 rows' worth of levels back -- an estimate that only affects the padding.
   std::vector<int32_t> order(n);
   for (int32_t r = 0; r < n; ++r)
     order[r] = r;
+  std::vector<int32_t> level_rows(n_levels + 1, 0);
+  for (int32_t r = 0; r < n; ++r)
+    ++level_rows[level[r] + 1];
+  for (int32_t l = 0; l < n_levels; ++l)
+    level_rows[l + 1] += level_rows[l]; // rows in levels < l + 1
+  std::vector<int32_t> key(n);
+  {
+    // the oldest level that can still hold fresh values for a row of level lv: walk back over about `groups` tiles
+    std::vector<int32_t> fresh_from(n_levels, 0);
+    for (int32_t lv = 0; lv < n_levels; ++lv)
+      {
+        int32_t l = lv, tiles = 0;
+        while (l > 0 && tiles < opt.groups)
+          {
+            --l;
+            tiles += (level_rows[l + 1] - level_rows[l] + opt.group_rows - 1) / opt.group_rows;
+          }
+        fresh_from[lv] = l;
+      }
+    for (int32_t r = 0; r < n; ++r)
+      {
+        int32_t n_fresh = 0;
+        for (int32_t k = first(r); k < last(r); ++k)
+          n_fresh += level[col[k]] >= fresh_from[level[r]];
+        key[r] = (((len_of(r) - n_fresh + 3) / 4) << 8) | ((n_fresh + 3) / 4);
+      }
+  }
   std::sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
     if (level[a] != level[b])
       return level[a] < level[b];
-    const int32_t la = len_of(a), lb = len_of(b);
-    if (la != lb)
-      return la > lb;
+    if (key[a] != key[b])
+      return key[a] > key[b];
     return a < b;
   });
   P.position.assign(n, -1);
@@ -161,8 +190,13 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
             int32_t add = 0;
             for (int32_t k = first(r); k < last(r); ++k) // far records, at most (the tile ends at p + group_rows at the latest)
               add += P.position[col[k]] < p + opt.group_rows - opt.window ? 16 : 0;
-            if (rows % 32 == 0)           // a new warp: its longest row comes first
-              add += 128 + warp_head + kWaveChunkBytes * ((len_of(r) + 3) / 4 + 1);
+            if (rows % 32 == 0) // a new warp: room for its longest row, old and fresh entries rounded up separately
+              {
+                int32_t longest = 0;
+                for (int32_t k2 = p + rows; k2 < std::min(n, p + rows + 32) && level[order[k2]] == lv; ++k2)
+                  longest = std::max(longest, len_of(order[k2]));
+                add += 128 + warp_head + kWaveChunkBytes * ((longest + 3) / 4 + 1);
+              }
             if (round_up(bytes + add, 128) > opt.max_tile_bytes)
               {
                 if (rows == 0)
