@@ -26,12 +26,17 @@ import __graft_entry__ as ge  # noqa: E402
 
 REYNOLDS = {"cylinderextruded": 100.0, "cylinder3d": 20.0, "nsbench2": 100.0}
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch group from the committed `ncu --set full` captures
-# (profiles/prof_*_r01_raw.csv), keyed by (mesh, refines, kernel); other workloads report null
-NCU_TRAFFIC = {
-    ("cylinderextruded", 1, "ilu_apply_pres"): 61.141248e6 + 0.974080e6 + 61.174528e6 + 1.096960e6,  # forward + backward sweep
-    ("cylinderextruded", 1, "spmv_pres"): 58.408448e6 + 0.525312e6,
-}
+def ncu_traffic(workload, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per application of `kernel` on `workload`, from the summaries of the
+    committed `ncu --set full` captures (profiles/ncu_traffic.json, written by tools/ncu_summary.py); None if that
+    kernel was not captured on that workload."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(path):
+        return None
+    with open(path) as f:
+        table = json.load(f)
+    entry = table.get(workload, {}).get(kernel)
+    return entry["dram_bytes"] if entry else None
 
 
 def parse_args():
@@ -46,6 +51,8 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernels", action="store_true", help="skip the per-kernel roofline pass")
+    ap.add_argument("--no-parity", action="store_true", help="skip the field comparison with the CPU oracle")
+    ap.add_argument("--parity-steps", type=int, default=0, help="steps compared with the oracle (default: 3 on one GPU, 2 on several)")
     ap.add_argument("--ilu-blocks", type=int, default=1,
                     help="GATED ALTERNATIVE (not the reference's preconditioner): ILU(0) of k index-range blocks")
     ap.add_argument("--deadline", type=int, default=600, help="abort the whole run after this many seconds")
@@ -119,38 +126,88 @@ def build_disc(pkg, args):
     return pkg.Disc(mesh_file, args.dim, params), params
 
 
+def preconditioner_label(args, world):
+    if args.ilu_blocks > 1:
+        return "GATED ALTERNATIVE: ILU(0) of %d index-range blocks" % args.ilu_blocks
+    if world > 1:
+        return ("block-local ILU(0) per rank (couplings to ghost DoFs dropped; NOT the reference's global SparseILU: "
+                "iteration counts differ from the single-GPU run)")
+    return "ILU(0) as the reference's SparseILU"
+
+
+def config_dict(args, disc, world):
+    """the same for both arms: it describes the workload, not who runs it"""
+    dim = disc.dim
+    return {"workload": workload_name(args), "dof": dim * disc.nv + disc.np_, "n_vel_per_component": disc.nv, "n_pres": disc.np_,
+            "cells": disc.n_cells, "preconditioner": preconditioner_label(args, world),
+            # every S35_* switch that was set: a line measured with a non-default path says so
+            "switches": {k: v for k, v in sorted(os.environ.items()) if k.startswith("S35_")},
+            "parallelism": ("mesh partition x%d (coordinate bisection, NCCL ghost exchange + all-reduce, "
+                            "block-local ILU(0))" % world) if world > 1 else "single GPU",
+            "l2": "working set (%.0f MB of matrices) exceeds L2; kernel benchmarks flush L2 between launches"
+                  % ((disc.info.nnz_vel_constrained * (dim + 1) * 8 + disc.info.nnz_vel_constrained * 4) / 1e6)}
+
+
+def field_differences(pkg, disc, reynolds, u_a, p_a, u_b, p_b):
+    """largest and l2 difference of two states relative to the second one's norms, and of their drag / lift"""
+    out = {}
+    du = max(np.abs(a - b).max() for a, b in zip(u_a, u_b))
+    out["u_rel_max"] = float(du / max(max(np.abs(b).max() for b in u_b), 1e-300))
+    out["u_rel_l2"] = float(np.sqrt(sum(((a - b) ** 2).sum() for a, b in zip(u_a, u_b)) / max(sum((b ** 2).sum() for b in u_b), 1e-300)))
+    out["p_rel_max"] = float(np.abs(p_a - p_b).max() / max(np.abs(p_b).max(), 1e-300))
+    out["p_rel_l2"] = float(np.sqrt(((p_a - p_b) ** 2).sum() / max((p_b ** 2).sum(), 1e-300)))
+    cd_a = disc.drag_lift(reynolds, np.concatenate(u_a), p_a)
+    cd_b = disc.drag_lift(reynolds, np.concatenate(u_b), p_b)
+    out["cd_cl"] = [float(x) for x in cd_b]
+    out["cd_cl_abs"] = float(np.abs(cd_a - cd_b).max())
+    return out
+
+
 def iteration_counts(c, dim):
     return {"gmres": [c.solver_stats(d).iterations for d in range(dim)], "cg": c.solver_stats(-1).iterations}
 
 
-def cpu_arm(pkg, disc, args, budget_seconds, steps=None, warmup=0):
-    """The oracle (-O3 -march=native, OpenMP over cells / components / rows like the reference's TBB use) on
-    the host cores.  Returns steps/s over a bounded sample."""
-    import oracle_binding as ob
+class CpuArm:
+    """The oracle (-O3 -march=native, OpenMP over cells / components / rows like the reference's TBB use) on the host
+    cores, advanced from the initial state like the device run."""
 
-    cores = os.cpu_count() or 1
-    orc = ob.Oracle(disc.problem, fast=True, threads=cores)
-    orc.set_field(pkg.PRES_N, disc.initial_pressure)
-    orc.set_field(pkg.PRES_N_MINUS_1, disc.initial_pressure)
-    n = 2
-    for _ in range(warmup):
-        orc.advance(n, 1)
-        n += 1
-    done, t0 = 0, time.perf_counter()
-    while True:
-        orc.advance(n, 1)
-        n += 1
-        done += 1
-        elapsed = time.perf_counter() - t0
-        if steps is not None:
-            if done >= steps:
+    def __init__(self, pkg, disc):
+        import oracle_binding as ob
+
+        self.pkg, self.disc = pkg, disc
+        self.cores = os.cpu_count() or 1
+        self.orc = ob.Oracle(disc.problem, fast=True, threads=self.cores)
+        self.orc.set_field(pkg.PRES_N, disc.initial_pressure)
+        self.orc.set_field(pkg.PRES_N_MINUS_1, disc.initial_pressure)
+        self.n = 2
+
+    def advance(self, steps):
+        for _ in range(steps):
+            self.orc.advance(self.n, 1)
+            self.n += 1
+
+    def state(self):
+        pkg = self.pkg
+        return [self.orc.get_field(pkg.U_N, d) for d in range(self.disc.dim)], self.orc.get_field(pkg.PRES_N)
+
+    def timed(self, budget_seconds, steps=None):
+        """steps/s over a bounded sample of steady steps (whatever was advanced before is the warm-up)"""
+        sec0 = {s: self.orc.section_seconds(s) for s in self.pkg.SECTIONS}
+        done, t0 = 0, time.perf_counter()
+        while True:
+            self.advance(1)
+            done += 1
+            elapsed = time.perf_counter() - t0
+            if steps is not None:
+                if done >= steps:
+                    break
+            elif elapsed >= budget_seconds or done >= 50:
                 break
-        elif elapsed >= budget_seconds or done >= 50:
-            break
-    sections = {s: orc.section_seconds(s) for s in pkg.SECTIONS}
-    its = iteration_counts(orc, disc.dim)
-    orc.close()
-    return done / elapsed, cores, done, sections, its
+        sections = {s: self.orc.section_seconds(s) - sec0[s] for s in self.pkg.SECTIONS}
+        return done / elapsed, done, sections, iteration_counts(self.orc, self.disc.dim)
+
+    def close(self):
+        self.orc.close()
 
 
 def main():
@@ -190,19 +247,27 @@ def main():
             return 0
         disc, _ = build_disc(pkg, args)
         dof = disc.dim * disc.nv + disc.np_
-        rate, cores, done, sections, its = cpu_arm(pkg, disc, args, args.cpu_seconds, steps=args.steps, warmup=args.warmup)
+        arm = CpuArm(pkg, disc)
+        arm.advance(args.warmup)
+        rate, done, sections, its = arm.timed(args.cpu_seconds, steps=args.steps)
+        cores = arm.cores
+        arm.close()
         line = {
             "impl": "reference", "metric": "time_steps_per_s", "value": rate, "unit": "steps/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / rate, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(args), "dof": dof, "n_vel_per_component": disc.nv, "n_pres": disc.np_},
-            "dof_steps_per_s": rate * dof, "iterations": its,
+            "config": config_dict(args, disc, args.gpus),
+            "dof_steps_per_s": rate * dof,
             "cpu_baseline": {"value": rate, "unit": "steps/s", "cores": cores, "kind": "port",
                              "sample": "%d warm-up + %d timed steps of the same workload; oracle/oracle.cpp built -O3 "
                                        "-march=native with OpenMP (the reference needs deal.II: unavailable on this box)"
                                        % (args.warmup, done)},
             "e2e": {"value": rate, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "sections_s": sections,
+            # what this process mapped of the repository's own native code: the host-only set-up library and the oracle
+            "native_libraries": sorted({os.path.basename(ln.split()[-1]) for ln in open("/proc/self/maps")
+                                        if ROOT in ln and ".so" in ln}),
+            "iterations": its,
         }
         emit(line)
         return 0
@@ -246,8 +311,49 @@ def main():
     ctx.set_field(pkg.PRES_N, initial_pressure)
     ctx.set_field(pkg.PRES_N_MINUS_1, initial_pressure)
 
-    # ---- device-resident run: W warm-up steps, then exactly K timed steps
+    # ---- parity on the benchmarked workload: the first steps from the initial state on the device and in the CPU oracle
+    # (rank 0; the oracle always solves the unpartitioned problem with the reference's global ILU(0)), fields compared by
+    # global DoF index.  These steps double as warm-up for both arms.
     n = 2
+    parity, cpu = None, None
+    want_cpu = rank == 0 and not args.no_cpu_baseline
+    if not args.no_parity:
+        p_steps = args.parity_steps or (3 if world == 1 else 2)
+        ctx.advance(n, p_steps)
+        n += p_steps
+        its_gpu = iteration_counts(ctx, dim)
+        u_own = [ctx.get_field(pkg.U_N, d) for d in range(dim)]
+        p_own = ctx.get_field(pkg.PRES_N)
+        if world > 1:
+            # every rank contributes the entries it owns (the first nv_owned / np_owned of its local vectors)
+            gathered = [None] * world if rank == 0 else None
+            mine = {"vel": np.array(part.vel_global[:part.nv_owned]), "pres": np.array(part.pres_global[:part.np_owned]),
+                    "u": [u[:part.nv_owned].copy() for u in u_own], "p": p_own[:part.np_owned].copy()}
+            dist.gather_object(mine, gathered, dst=0)
+            if rank == 0:
+                u_dev = [np.zeros(disc.nv) for _ in range(dim)]
+                p_dev = np.zeros(disc.np_)
+                for g in gathered:
+                    for d in range(dim):
+                        u_dev[d][g["vel"]] = g["u"][d]
+                    p_dev[g["pres"]] = g["p"]
+        else:
+            u_dev, p_dev = u_own, p_own
+        if rank == 0:
+            cpu = CpuArm(pkg, disc)
+            cpu.advance(p_steps)
+            u_cpu, p_cpu = cpu.state()
+            parity = field_differences(pkg, disc, REYNOLDS.get(args.mesh, 100.0), u_dev, p_dev, u_cpu, p_cpu)
+            parity.update({"steps": p_steps, "its_gpu": its_gpu, "its_cpu": iteration_counts(cpu.orc, dim),
+                           "against": "oracle/oracle.cpp from the same initial state (global ILU(0), one process)",
+                           "note": "the solvers stop at eps * ||rhs||: fields agree to about eps x condition number "
+                                   "(BASELINE.md section 4), drag/lift to 1e-6"})
+            if not want_cpu:
+                cpu.close()
+                cpu = None
+        barrier()
+
+    # ---- device-resident run: W warm-up steps, then exactly K timed steps
     if args.warmup:
         ctx.advance(n, args.warmup)
         n += args.warmup
@@ -342,7 +448,7 @@ def main():
         dominant = max(per_step, key=per_step.get)
         k = kernels[dominant]
         roofline = {"kernel": dominant, "bound": "hbm", "achieved": k["GB/s"], "peak": peak, "unit": "GB/s",
-                    "frac": k["frac"], "traffic": NCU_TRAFFIC.get((args.mesh, args.refines, dominant)) if world == 1 else None,
+                    "frac": k["frac"], "traffic": ncu_traffic(workload_name(args), dominant) if world == 1 else None,
                     "algorithmic_bytes": k["algorithmic_bytes"], "ms": k["ms"], "launches": k["launches"],
                     "peak_source": peak_kind,
                     "share_of_step": per_step[dominant] / (1e3 * elapsed / args.steps),
@@ -350,12 +456,19 @@ def main():
                     if dominant.startswith("ilu") else ""}
 
     cpu_baseline = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        rate, cores, done, cpu_sections, cpu_its = cpu_arm(pkg, disc, args, args.cpu_seconds)
-        cpu_baseline = {"value": rate, "unit": "steps/s", "cores": cores, "kind": "port",
-                        "sample": "%d time steps of the same workload from the same initial state (oracle/oracle.cpp, "
-                                  "-O3 -march=native, OpenMP)" % done,
+    if want_cpu and world == 1:
+        if cpu is None:
+            cpu = CpuArm(pkg, disc)
+        # steady steps only, like the device arm: whatever the parity run did not cover of the warm-up comes first
+        cpu.advance(max(0, args.warmup - (cpu.n - 2)))
+        warm = cpu.n - 2
+        rate, done, cpu_sections, cpu_its = cpu.timed(args.cpu_seconds)
+        cpu_baseline = {"value": rate, "unit": "steps/s", "cores": cpu.cores, "kind": "port",
+                        "sample": "%d timed time steps of the same workload after %d warm-up steps from the same initial "
+                                  "state (oracle/oracle.cpp, -O3 -march=native, OpenMP)" % (done, warm),
                         "sections_s_per_step": {k: v / done for k, v in cpu_sections.items()}, "iterations": cpu_its}
+    if cpu is not None:
+        cpu.close()
 
     if rank == 0:
         line = {
@@ -363,20 +476,13 @@ def main():
             "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / args.steps, "higher_is_better": True,
             # one mesh of fixed size is partitioned over the ranks: the total work does not grow with N
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(args), "dof": dof, "n_vel_per_component": disc.nv, "n_pres": disc.np_,
-                       "cells": disc.n_cells,
-                       "preconditioner": "ILU(0) as the reference's SparseILU" if args.ilu_blocks <= 1 else
-                                         "GATED ALTERNATIVE: ILU(0) of %d index-range blocks" % args.ilu_blocks,
-                       # every S35_* switch that was set: a line measured with a non-default path says so
-                       "switches": {k: v for k, v in sorted(os.environ.items()) if k.startswith("S35_")},
-                       "parallelism": ("mesh partition x%d (coordinate bisection, NCCL ghost exchange + all-reduce, "
-                                       "block-local ILU(0))" % world) if world > 1 else "single GPU",
-                       "l2": "working set (%.0f MB of matrices) exceeds L2; kernel benchmarks flush L2 between launches"
-                             % ((disc.info.nnz_vel_constrained * (dim + 1) * 8 + disc.info.nnz_vel_constrained * 4) / 1e6)},
-            "dof_steps_per_s": value * dof, "iterations": its, "wall_ms_per_step": 1e3 * wall_s / args.steps,
+            "config": config_dict(args, disc, world),
+            "dof_steps_per_s": value * dof, "wall_ms_per_step": 1e3 * wall_s / args.steps,
             "sections_ms_per_step": sections, "gpu_launches": launches, "clocks": clocks, "e2e": e2e, "roofline": roofline,
             "kernels": kernels, "cpu_baseline": cpu_baseline,
             "setup_s": {"host_discretisation": disc.info.setup_seconds, "device_context": ctx_seconds},
+            # last, so that a truncated tail of the line keeps them
+            "iterations": its, "parity": parity,
         }
         emit(line)
     ctx.close()

@@ -14,6 +14,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libstep35a_b200.so")
+HOST_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libstep35a_host.so")
 
 c_double_p = C.POINTER(C.c_double)
 c_int32_p = C.POINTER(C.c_int32)
@@ -177,6 +178,10 @@ _SIGNATURES = [
     ("s35_disc_drag_lift", C.c_int, [_VP, C.c_double, c_double_p, c_double_p, c_double_p]),
 ]
 DECLARED_SYMBOLS = [s[0] for s in _SIGNATURES]
+# what libstep35a_host.so (set-up, partition, drag / lift: no device code, links no CUDA library) exports
+HOST_ONLY_SYMBOLS = ["s35_last_error"] + [s[0] for s in _SIGNATURES
+                                          if s[0].startswith(("s35_params_", "s35_disc_", "s35_part_", "s35_mesh_"))]
+_host_lib = None
 
 
 def lib():
@@ -195,9 +200,33 @@ def lib():
     return _lib
 
 
+def host_lib():
+    """The host-only library: discretisation, partition and drag / lift.  Everything that only sets a problem up goes
+    through it, so that a process that never touches a GPU (the CPU reference arm of bench.py, the oracle tests) maps
+    no CUDA library."""
+    global _host_lib
+    if _host_lib is None:
+        if not os.path.exists(HOST_LIB_PATH):
+            raise ImportError("libstep35a_host.so is not built (%s); run `python -c 'import __graft_entry__ as g; "
+                              "g.build()'`" % HOST_LIB_PATH)
+        handle = C.CDLL(HOST_LIB_PATH)
+        for name, restype, argtypes in _SIGNATURES:
+            if name in HOST_ONLY_SYMBOLS:
+                fn = getattr(handle, name)
+                fn.restype = restype
+                fn.argtypes = argtypes
+        _host_lib = handle
+    return _host_lib
+
+
 def check(status):
     if status != 0:
         raise S35Error(status, lib().s35_last_error().decode())
+
+
+def check_host(status):
+    if status != 0:
+        raise S35Error(status, host_lib().s35_last_error().decode())
 
 
 def dptr(a):
@@ -226,7 +255,7 @@ def launch_count():
 
 def default_params(**overrides):
     p = Params()
-    lib().s35_params_defaults(C.byref(p))
+    host_lib().s35_params_defaults(C.byref(p))
     for k, v in overrides.items():
         setattr(p, k, v)
     return p
@@ -234,7 +263,7 @@ def default_params(**overrides):
 
 def read_params(prm_file, **overrides):
     p = Params()
-    check(lib().s35_params_read(prm_file.encode(), C.byref(p)))
+    check_host(host_lib().s35_params_read(prm_file.encode(), C.byref(p)))
     for k, v in overrides.items():
         setattr(p, k, v)
     return p
@@ -242,7 +271,7 @@ def read_params(prm_file, **overrides):
 
 def parse_params(text):
     p = Params()
-    check(lib().s35_params_parse(text.encode(), C.byref(p)))
+    check_host(host_lib().s35_params_parse(text.encode(), C.byref(p)))
     return p
 
 
@@ -263,22 +292,22 @@ class Disc:
             self._owns = False
         else:
             h = _VP()
-            check(lib().s35_disc_create(mesh_file.encode(), dim, C.byref(params), C.byref(h)))
+            check_host(host_lib().s35_disc_create(mesh_file.encode(), dim, C.byref(params), C.byref(h)))
             self.handle = h
             self._owns = True
         self.info = DiscInfo()
-        check(lib().s35_disc_get_info(self.handle, C.byref(self.info)))
-        self.problem = lib().s35_disc_problem(self.handle)  # POINTER(Problem)
+        check_host(host_lib().s35_disc_get_info(self.handle, C.byref(self.info)))
+        self.problem = host_lib().s35_disc_problem(self.handle)  # POINTER(Problem)
         p = self.problem.contents
         self.dim, self.n_cells, self.nv, self.np_ = p.dim, p.n_cells, p.n_vel, p.n_pres
         dim = self.dim
-        self.vel_support = _view(lib().s35_disc_support_points(self.handle, 0), (self.nv, dim), np.float64)
-        self.pres_support = _view(lib().s35_disc_support_points(self.handle, 1), (self.np_, dim), np.float64)
-        self.initial_pressure = _view(lib().s35_disc_initial_pressure(self.handle), (self.np_,), np.float64)
+        self.vel_support = _view(host_lib().s35_disc_support_points(self.handle, 0), (self.nv, dim), np.float64)
+        self.pres_support = _view(host_lib().s35_disc_support_points(self.handle, 1), (self.np_, dim), np.float64)
+        self.initial_pressure = _view(host_lib().s35_disc_initial_pressure(self.handle), (self.np_,), np.float64)
 
     def close(self):
         if self._owns and self.handle is not None:
-            lib().s35_disc_destroy(self.handle)
+            host_lib().s35_disc_destroy(self.handle)
         self.handle = None
 
     def __del__(self):
@@ -316,12 +345,12 @@ class Disc:
         verts = _view(p.cell_vertices, (self.n_cells, vpc, self.dim), np.float64)
         dofs = _view(p.vel_cell_dofs, (self.n_cells, dpc), np.int32)
         color = _view(p.cell_color, (self.n_cells,), np.int32)
-        pdofs = _view(lib().s35_disc_pres_cell_dofs(self.handle), (self.n_cells, vpc), np.int32)
+        pdofs = _view(host_lib().s35_disc_pres_cell_dofs(self.handle), (self.n_cells, vpc), np.int32)
         return verts, dofs, color, pdofs
 
     def mesh(self):
         v, c, b, ids, nb = c_double_p(), c_int32_p(), c_int32_p(), c_int32_p(), C.c_int64()
-        check(lib().s35_disc_mesh(self.handle, C.byref(v), C.byref(c), C.byref(b), C.byref(ids), C.byref(nb)))
+        check_host(host_lib().s35_disc_mesh(self.handle, C.byref(v), C.byref(c), C.byref(b), C.byref(ids), C.byref(nb)))
         vpc, vpf = 1 << self.dim, 1 << (self.dim - 1)
         return (_view(v, (self.info.n_vertices, self.dim), np.float64), _view(c, (self.n_cells, vpc), np.int32),
                 _view(b, (nb.value, vpf), np.int32), _view(ids, (nb.value,), np.int32))
@@ -330,7 +359,7 @@ class Disc:
         out = np.zeros(2)
         u = f64(u)
         p = f64(p)
-        check(lib().s35_disc_drag_lift(self.handle, reynolds, dptr(u), dptr(p), dptr(out)))
+        check_host(host_lib().s35_disc_drag_lift(self.handle, reynolds, dptr(u), dptr(p), dptr(out)))
         return out
 
 
@@ -339,10 +368,10 @@ class Part:
 
     def __init__(self, disc, n_ranks, rank):
         h = _VP()
-        check(lib().s35_part_create(disc.handle, n_ranks, rank, C.byref(h)))
+        check_host(host_lib().s35_part_create(disc.handle, n_ranks, rank, C.byref(h)))
         self.handle = h
         self.disc = disc
-        self.problem = lib().s35_part_problem(h)
+        self.problem = host_lib().s35_part_problem(h)
         p = self.problem.contents
         d = p.dist.contents
         self.rank, self.n_ranks, self.dim = d.rank, d.n_ranks, p.dim
@@ -350,7 +379,7 @@ class Part:
         self.nv_owned, self.np_owned = d.n_vel_owned, d.n_pres_owned
         self.vel_global = _view(d.vel_global_index, (self.nv,), np.int32)
         self.pres_global = _view(d.pres_global_index, (self.np_,), np.int32)
-        self.initial_pressure = _view(lib().s35_part_initial_pressure(h), (self.np_,), np.float64)
+        self.initial_pressure = _view(host_lib().s35_part_initial_pressure(h), (self.np_,), np.float64)
 
     def halo(self, which):
         d = self.problem.contents.dist.contents
@@ -383,7 +412,7 @@ class Part:
 
     def close(self):
         if self.handle is not None:
-            lib().s35_part_destroy(self.handle)
+            host_lib().s35_part_destroy(self.handle)
         self.handle = None
 
     def __del__(self):
@@ -645,7 +674,7 @@ def vec_add_and_dot(a, x, y, w):
 
 
 def mesh_convert(in_file, dim, out_file):
-    check(lib().s35_mesh_convert(in_file.encode(), dim, out_file.encode()))
+    check_host(host_lib().s35_mesh_convert(in_file.encode(), dim, out_file.encode()))
 
 
 class Simulation:

@@ -429,6 +429,10 @@ s35_status s35_ctx_get_operator_values(s35_ctx *ctx, s35_operator op, int32_t co
         break;
       case S35_VEL_ILU:
         S35_REQUIRE(component >= 0 && component < c.dim, "component out of range");
+        // with ilu_blocks > 1 or on a partition the factor lives on a filtered pattern (fewer entries, other positions):
+        // there is no value array on the caller's pattern to hand out
+        if (c.use_blocks)
+          throw Error(S35_ERR_UNSUPPORTED, "the ILU factor of a block / partitioned preconditioner is not on the matrix pattern");
         src = c.prec_vel[component].lu;
         break;
       default: throw Error(S35_ERR_INVALID, "unknown operator id");
@@ -514,11 +518,17 @@ s35_status s35_ctx_bench_kernel(s35_ctx *ctx, s35_bench_kernel kernel, int32_t w
     const double *us[3] = {c.u_star[0], c.u_star[1], c.u_star[2]};
     const double *gvals[3] = {c.gradT_val[0], c.gradT_val[1], c.gradT_val[2]};
     const double *gx[3] = {xv, yv, zv};
+    // what prec_vel[0] factorises: the iteration matrix's values, gathered onto the block pattern when the factor lives
+    // there (ilu_blocks > 1, or a partition) -- as Ctx::solve_component does
+    auto factor_input = [&]() -> const double * {
+      vec_copy(c.it_val[0], c.vel_adv.val, c.vel_adv.nnz, s);
+      if (!c.use_blocks)
+        return c.it_val[0];
+      gather_values(c.blk_val[0], c.it_val[0], c.vel_blk_src, c.vel_blk.nnz, s);
+      return c.blk_val[0];
+    };
     if ((kernel == S35_BENCH_ILU_APPLY_VEL) && !c.prec_vel[0].factored)
-      {
-        vec_copy(c.it_val[0], c.vel_adv.val, c.vel_adv.nnz, s);
-        c.prec_vel[0].factor(c.it_val[0], c.diag_strength, s);
-      }
+      c.prec_vel[0].factor(factor_input(), c.diag_strength, s);
     std::function<void()> run;
     switch (kernel)
       {
@@ -559,9 +569,11 @@ s35_status s35_ctx_bench_kernel(s35_ctx *ctx, s35_bench_kernel kernel, int32_t w
         run = [&] { vec_add_and_dot(c.scal.ptr + 6, yv, DScal(1e-9), xv, zv, c.nv, kSum, c.ws, s); };
         break;
       case S35_BENCH_ILU_FACTOR_VEL:
-        bytes = 20.0 * c.vel_adv.nnz;
-        run = [&] { c.prec_vel[0].factor(c.it_val[0], c.diag_strength, s); };
-        vec_copy(c.it_val[0], c.vel_adv.val, c.vel_adv.nnz, s);
+        bytes = 20.0 * (c.use_blocks ? c.vel_blk.nnz : c.vel_adv.nnz);
+        {
+          const double *input = factor_input();
+          run = [&c, input, s] { c.prec_vel[0].factor(input, c.diag_strength, s); };
+        }
         break;
       default: throw Error(S35_ERR_INVALID, "unknown bench kernel");
       }

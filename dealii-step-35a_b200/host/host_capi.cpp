@@ -8,8 +8,17 @@
 #include <memory>
 #include <stdexcept>
 
+// S35_HOST_ONLY: the build of this file that goes into libstep35a_host.so (set-up, partition, drag / lift; no device
+// code, no simulation driver).  It keeps its own error string.
 namespace s35 {
+#ifdef S35_HOST_ONLY
+namespace {
+thread_local std::string g_host_last_error;
+}
+void set_last_error(const std::string &msg) { g_host_last_error = msg; }
+#else
 void set_last_error(const std::string &msg); // csrc/capi.cu
+#endif
 void drag_lift(const Discretization &D, double reynolds, const double *u, const double *p, double *out);
 }
 
@@ -29,6 +38,7 @@ struct s35_part
   std::unique_ptr<s35::LocalProblem> L;
 };
 
+#ifndef S35_HOST_ONLY
 struct s35_sim
 {
   int dim = 0;
@@ -36,6 +46,7 @@ struct s35_sim
   std::unique_ptr<Step35::NavierStokesProjection<3>> sim3;
   s35_disc disc_view; // non-owning view for s35_sim_disc
 };
+#endif
 
 namespace {
 
@@ -277,6 +288,7 @@ s35_status s35_mesh_convert(const char *in_file, int32_t dim, const char *out_fi
     S35_ERR_IO);
 }
 
+#ifndef S35_HOST_ONLY
 s35_status s35_sim_create(const s35_params *params, const char *mesh_file, int32_t dim, s35_sim **out)
 {
   return guarded([&] {
@@ -330,6 +342,8 @@ int32_t s35_sim_n_steps(const s35_sim *sim)
   return (int32_t)(sim->dim == 2 ? sim->sim2->n_time_steps() : sim->sim3->n_time_steps());
 }
 
+#endif
+
 s35_status s35_disc_drag_lift(const s35_disc *d, double reynolds, const double *u, const double *p, double *out)
 {
   return guarded([&] {
@@ -339,6 +353,7 @@ s35_status s35_disc_drag_lift(const s35_disc *d, double reynolds, const double *
   });
 }
 
+#ifndef S35_HOST_ONLY
 s35_status s35_sim_drag_lift(s35_sim *sim, double *out)
 {
   return guarded([&] {
@@ -356,5 +371,8 @@ s35_status s35_sim_drag_lift(s35_sim *sim, double *out)
     s35::drag_lift(D, pr.reynolds, u.data(), p.data(), out);
   });
 }
+#else
+const char *s35_last_error(void) { return s35::g_host_last_error.c_str(); }
+#endif
 
 } // extern "C"

@@ -31,6 +31,29 @@ def test_library_exports_every_declared_symbol(pkg):
     assert missing == []
 
 
+def test_host_only_library_exports_the_set_up_entry_points_and_links_no_cuda(pkg):
+    """libstep35a_host.so: what the CPU reference arm of bench.py and the oracle tests load instead of the CUDA library"""
+    import subprocess
+    handle = ctypes.CDLL(pkg.HOST_LIB_PATH)
+    assert [s for s in pkg.HOST_ONLY_SYMBOLS if not hasattr(handle, s)] == []
+    assert not hasattr(handle, "s35_ctx_create") and not hasattr(handle, "s35_sim_run")
+    out = subprocess.run(["ldd", pkg.HOST_LIB_PATH], capture_output=True, text=True).stdout
+    assert "cuda" not in out.lower() and "nccl" not in out.lower()
+    dynsyms = subprocess.run(["nm", "-D", "--undefined-only", pkg.HOST_LIB_PATH], capture_output=True, text=True).stdout
+    assert "cuda" not in dynsyms.lower()
+
+
+def test_setting_a_problem_up_does_not_load_the_cuda_library():
+    """a fresh interpreter that builds a discretisation maps libstep35a_host.so only"""
+    import subprocess
+    import sys
+    code = ("import sys, os; sys.path.insert(0, %r); import __graft_entry__ as ge; pkg = ge.load_package(); "
+            "d = pkg.Disc(os.path.join(%r, 'meshes', 'nsbench2.s35m'), 2, pkg.default_params(vel_off_diagonals=0)); "
+            "maps = open('/proc/self/maps').read(); print('libstep35a_b200' in maps, 'libstep35a_host' in maps)") % (ROOT, ROOT)
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True)
+    assert out.stdout.split() == ["False", "True"], out.stdout + out.stderr
+
+
 def test_binding_covers_every_declared_symbol(pkg):
     assert sorted(set(pkg.DECLARED_SYMBOLS)) == declared_symbols()
 

@@ -20,6 +20,10 @@ def test_reference_arm_prints_one_json_line():
     assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
     assert line["e2e"] == {"value": line["value"], "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert line["config"]["workload"].startswith("nsbench2 r1") and line["dtype"] == "f64"
+    # the arm maps the host-only set-up library and the oracle, not the CUDA library
+    assert "libstep35a_host.so" in line["native_libraries"] and "libstep35a_b200.so" not in line["native_libraries"]
+    assert set(line["config"]) == {"workload", "dof", "n_vel_per_component", "n_pres", "cells", "preconditioner", "switches",
+                                   "parallelism", "l2"}
 
 
 def test_reference_arm_is_silent_on_other_ranks():

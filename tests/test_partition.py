@@ -45,7 +45,7 @@ def test_ownership_and_halo_plans_are_consistent(pkg, make_disc, mesh, dim, refi
     # balanced cells, every cell assigned
     cell_rank = np.zeros(disc.n_cells, np.int32)
     import ctypes as C
-    pkg.check(pkg.lib().s35_disc_partition_cells(disc.handle, n_ranks, cell_rank.ctypes.data_as(C.POINTER(C.c_int32))))
+    pkg.check_host(pkg.host_lib().s35_disc_partition_cells(disc.handle, n_ranks, cell_rank.ctypes.data_as(C.POINTER(C.c_int32))))
     counts = np.bincount(cell_rank, minlength=n_ranks)
     assert counts.sum() == disc.n_cells and counts.max() - counts.min() <= 1
 
