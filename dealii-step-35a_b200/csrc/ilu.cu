@@ -262,26 +262,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
                "r"(parity)
                : "memory");
 }
-// the same by polling: a thread suspended in try_wait was measured to hold up other warps' shared-memory
-// instructions on its scheduler, so the producer (which waits most of the time) polls and sleeps instead
-__device__ __forceinline__ void mbar_wait_polling(uint64_t *bar, uint32_t parity)
-{
-  for (;;)
-    {
-      uint32_t done;
-      asm volatile("{\n"
-                   ".reg .pred p;\n"
-                   "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-                   "selp.u32 %0, 1, 0, p;\n"
-                   "}"
-                   : "=r"(done)
-                   : "r"(smem_addr(bar)), "r"(parity)
-                   : "memory");
-      if (done)
-        return;
-      __nanosleep(64);
-    }
-}
 // global -> shared bulk copy (16-byte aligned, a multiple of 16 bytes) that reports to an mbarrier
 __device__ __forceinline__ void bulk_copy_to_shared(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
 {
@@ -307,14 +287,13 @@ __device__ __forceinline__ void group_signal(int tile, int threads)
 struct WaveArgs
 {
   const unsigned char *blob;
-  const int4 *directory;
-  const int2 *desc;
-  const int32_t *rhs_index;
+  const int4 *directory;  // per tile: blob offset / 16, ring offset / 16, bytes, tile that must be finished before the load
+  const int2 *rhs_dir;    // per tile: offset (doubles) and size (bytes) of its right-hand sides in rhs layout
   int32_t n_tiles, groups, group_rows, window, ring_bytes;
-  const double *rhs;   // right-hand sides, indexed through the plan
-  double *by_position; // the sweep's result in position order (values that left the window; the next sweep's input)
-  double *natural;     // backward sweep: the result by row index
-  long long *trace;    // S35_WAVE_TRACE: per tile, the clock at four points of its first warp (else nullptr)
+  const double *rhs;      // right-hand sides in this sweep's rhs layout
+  double *by_position;    // the sweep's result in position order (read again for values that left the window)
+  double *next;           // forward sweep: the backward sweep's right-hand sides (its rhs layout); backward: the result by row
+  long long *trace;       // S35_WAVE_TRACING builds: per tile, clocks of its warps (else nullptr)
 };
 
 template <bool FORWARD>
@@ -325,6 +304,7 @@ __global__ void __launch_bounds__(kWaveMaxThreads, 1) k_wave_sweep(const WaveArg
   unsigned char *const ring = wave_smem + (size_t)a.window * 8;
   uint64_t *const full = reinterpret_cast<uint64_t *>(ring + a.ring_bytes);
   uint64_t *const empty = full + kWaveSlots;
+  int32_t *const ring_at = reinterpret_cast<int32_t *>(empty + kWaveSlots); // where in the ring the tile of a slot lies
   const int tid = threadIdx.x;
   const int n_consumers = a.groups * a.group_rows;
   if (tid == 0)
@@ -344,14 +324,18 @@ __global__ void __launch_bounds__(kWaveMaxThreads, 1) k_wave_sweep(const WaveArg
     {
       // producer: ONE thread issues the copies (no warp-wide instruction may sit between two copies: measured on
       // B200, a shuffle in this loop waited > 1000 cycles behind the consumers' barrier waits).  The directory is
-      // read eight tiles ahead.
+      // read four tiles ahead.
       if (tid != n_consumers)
         return;
-      constexpr int kAhead = 8;
+      constexpr int kAhead = 4;
       int4 dir[kAhead];
+      int2 rdir[kAhead];
 #pragma unroll
       for (int u = 0; u < kAhead; ++u)
-        dir[u] = u < a.n_tiles ? __ldg(a.directory + u) : make_int4(0, 0, 0, 0);
+        {
+          dir[u] = u < a.n_tiles ? __ldg(a.directory + u) : make_int4(0, 0, 0, 0);
+          rdir[u] = u < a.n_tiles ? __ldg(a.rhs_dir + u) : make_int2(0, 0);
+        }
       int freed = 0; // tiles known to be finished
       for (int base = 0; base < a.n_tiles; base += kAhead)
         {
@@ -362,20 +346,27 @@ __global__ void __launch_bounds__(kWaveMaxThreads, 1) k_wave_sweep(const WaveArg
               if (t >= a.n_tiles)
                 break;
               const int4 d = dir[u];
+              const int2 r = rdir[u];
               if (t + kAhead < a.n_tiles)
-                dir[u] = __ldg(a.directory + t + kAhead);
+                {
+                  dir[u] = __ldg(a.directory + t + kAhead);
+                  rdir[u] = __ldg(a.rhs_dir + t + kAhead);
+                }
               const int s = t % kWaveSlots;
               if (kWaveTracing && a.trace)
                 a.trace[24 * (size_t)t + 5] = clock64();
               while (freed <= d.w)
                 {
-                  mbar_wait_polling(empty + freed % kWaveSlots, (uint32_t)((freed / kWaveSlots) & 1));
+                  mbar_wait(empty + freed % kWaveSlots, (uint32_t)((freed / kWaveSlots) & 1));
                   ++freed;
                 }
               if (kWaveTracing && a.trace)
                 a.trace[24 * (size_t)t + 4] = clock64();
-              mbar_expect_tx(full + s, (uint32_t)d.z);
+              // tile and right-hand sides land side by side; one barrier counts both
+              ring_at[s] = d.y * 16;
+              mbar_expect_tx(full + s, (uint32_t)(d.z + r.y));
               bulk_copy_to_shared(ring + (size_t)d.y * 16, a.blob + (size_t)d.x * 16, (uint32_t)d.z, full + s);
+              bulk_copy_to_shared(ring + (size_t)d.y * 16 + d.z, a.rhs + r.x, (uint32_t)r.y, full + s);
             }
         }
       return;
@@ -385,63 +376,49 @@ __global__ void __launch_bounds__(kWaveMaxThreads, 1) k_wave_sweep(const WaveArg
   const int warp_first_row = i - lane;
   const int pair = 2 * a.group_rows; // threads on a tile's barrier: its own group arrives, the next tile's group waits
   const uint32_t mask = (uint32_t)a.window - 1u;
-  // Look-ahead without touching the ring, three global loads deep, each issued at the top of one of the group's tiles
-  // and used at the top of the next: a tile's descriptor three tiles ahead, the index of the row's right-hand side
-  // two tiles ahead, the right-hand side itself one tile ahead.
-  auto load_desc = [&](int t) { return t < a.n_tiles ? __ldg(a.desc + t) : make_int2(0, 0); };
-  auto load_index = [&](int2 d) { return i < (d.x & 511) ? __ldg(a.rhs_index + d.y + i) : -1; };
-  auto load_rhs = [&](int32_t index) { return index >= 0 ? ld_l2(a.rhs + index) : 0.0; };
-  int2 desc0 = load_desc(group), desc1 = load_desc(group + a.groups), desc2 = load_desc(group + 2 * a.groups);
-  int32_t index1 = load_index(desc1);
-  double rhs0 = load_rhs(load_index(desc0));
+  // The consumers read nothing from global memory (a pending global load holds a warp up at its next shared-memory
+  // result, however early it was issued): tile, right-hand sides and the tile's place in the ring all come through
+  // shared memory, behind the tile's `full` barrier.
   for (int t = group; t < a.n_tiles; t += a.groups)
     {
-      const int32_t desc = desc0.x, desc_first_pos = desc0.y;
-      const double rhs = rhs0;
-      rhs0 = load_rhs(index1);          // for tile t + groups
-      index1 = load_index(desc2);       // for tile t + 2 groups
-      desc0 = desc1;
-      desc1 = desc2;
-      desc2 = load_desc(t + 3 * a.groups);
-      const int rows = desc & 511;
       const int s = t % kWaveSlots;
+      if (kWaveTracing && a.trace && i == 0)
+        a.trace[24 * (size_t)t + 0] = clock64();
+      mbar_wait(full + s, (uint32_t)((t / kWaveSlots) & 1));
+      if (kWaveTracing && a.trace && i == 0)
+        a.trace[24 * (size_t)t + 1] = clock64();
+      const unsigned char *const tile = ring + ring_at[s];
+      const int4 head = *reinterpret_cast<const int4 *>(tile); // first position, rows, warps, n_far
+      const int rows = head.y, desc_first_pos = head.x;
       if (warp_first_row >= rows)
         {
           // no row for this warp: it only keeps the barriers' counts right
           if (t > 0)
             group_wait(t - 1, pair);
-          if (kWaveTracing && a.trace && lane == 0)
-            a.trace[24 * (size_t)t + 8 + (i >> 5)] = clock64();
           if (t + 1 < a.n_tiles)
             group_signal(t, pair);
-          if (kWaveTracing && a.trace && lane == 0)
-            a.trace[24 * (size_t)t + 16 + (i >> 5)] = clock64();
           if (lane == 0)
             mbar_arrive(empty + s);
           continue;
         }
       const bool tracing = kWaveTracing && a.trace != nullptr && i == 0;
-      if (tracing)
-        a.trace[24 * (size_t)t + 0] = clock64();
-      mbar_wait(full + s, (uint32_t)((t / kWaveSlots) & 1));
-      if (tracing)
-        a.trace[24 * (size_t)t + 1] = clock64();
-      const unsigned char *const tile = ring + (size_t)(desc >> 9) * 128;
-      const int4 head = *reinterpret_cast<const int4 *>(tile); // first position, rows, warps, n_far
       const uint32_t word = reinterpret_cast<const uint32_t *>(tile)[4 + (i >> 5)];
       const unsigned char *const block = tile + (size_t)(word >> 16) * 128;
       const int n_pre = (int)((word >> 8) & 0xffu), n_chunks = (int)(word & 0xffu);
       const bool active = i < rows;
-      constexpr int kHead = FORWARD ? 0 : kWaveBackwardHead;
+      constexpr int kHead = FORWARD ? kWaveForwardHead : kWaveBackwardHead;
+      const double rhs = reinterpret_cast<const double *>(tile + reinterpret_cast<const int32_t *>(tile)[12])[active ? i : 0];
       // this lane's first chunk: slots at +0, values 0-1 at +256, values 2-3 at +768; the next chunk 1280 bytes on
       const unsigned char *const lane_slots = block + kHead + 8 * lane;
       const unsigned char *const lane_vals = block + kHead + 256 + 16 * lane;
       double acc = 0.0, piv = 1.0, result = 0.0;
-      int32_t natural_row = 0;
-      if (!FORWARD)
+      int32_t scatter_to; // where the result goes in a.next
+      if (FORWARD)
+        scatter_to = reinterpret_cast<const int32_t *>(block)[lane];
+      else
         {
           piv = reinterpret_cast<const double *>(block)[lane];
-          natural_row = reinterpret_cast<const int32_t *>(block + 256)[lane];
+          scatter_to = reinterpret_cast<const int32_t *>(block + 256)[lane];
         }
       // one chunk: four products, the solution values straight from the window (the slots are byte offsets)
       struct Chunk
@@ -519,8 +496,7 @@ __global__ void __launch_bounds__(kWaveMaxThreads, 1) k_wave_sweep(const WaveArg
       if (active)
         {
           a.by_position[first_pos + i] = result;
-          if (!FORWARD)
-            a.natural[natural_row] = result;
+          a.next[scatter_to] = result;
         }
     }
 }
@@ -535,23 +511,27 @@ __global__ void k_wave_fill_values(int64_t n, const int32_t *__restrict__ dst, c
     stream[dst[i]] = lu[src[i]];
 }
 
-int env_int(const char *name, int fallback)
+// dst[slot[r]] = src[r]: the sweep's input into rhs layout
+__global__ void k_wave_to_layout(int32_t n, const int32_t *__restrict__ slot, const double *__restrict__ src, double *__restrict__ dst)
 {
-  const char *t = std::getenv(name);
-  return t && *t ? std::atoi(t) : fallback;
+  const int32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < n)
+    dst[slot[r]] = src[r];
 }
 
 void wave_launch(DevIlu &p, double *dst, const double *src, cudaStream_t s)
 {
   DevIlu::Wave &w = p.wave;
-  WaveArgs fwd{w.blob[0].ptr, reinterpret_cast<const int4 *>(w.directory[0].ptr), reinterpret_cast<const int2 *>(w.desc[0].ptr), w.rhs_index[0].ptr, w.n_tiles[0], w.groups, w.group_rows,
-               w.window, w.ring_bytes, src, w.by_position[0].ptr, nullptr, w.trace.ptr};
-  WaveArgs bwd{w.blob[1].ptr, reinterpret_cast<const int4 *>(w.directory[1].ptr), reinterpret_cast<const int2 *>(w.desc[1].ptr), w.rhs_index[1].ptr, w.n_tiles[1], w.groups, w.group_rows,
-               w.window, w.ring_bytes, w.by_position[0].ptr, w.by_position[1].ptr, dst, nullptr};
+  S35_LAUNCH(k_wave_to_layout, (p.n + 255) / 256, 256, 0, s, p.n, w.rhs_slot.ptr, src, w.rhs[0].ptr);
+  WaveArgs fwd{w.blob[0].ptr, reinterpret_cast<const int4 *>(w.directory[0].ptr), reinterpret_cast<const int2 *>(w.rhs_dir[0].ptr),
+               w.n_tiles[0], w.groups, w.group_rows, w.window, w.ring_bytes, w.rhs[0].ptr, w.by_position[0].ptr, w.rhs[1].ptr,
+               w.trace.ptr};
+  WaveArgs bwd{w.blob[1].ptr, reinterpret_cast<const int4 *>(w.directory[1].ptr), reinterpret_cast<const int2 *>(w.rhs_dir[1].ptr),
+               w.n_tiles[1], w.groups, w.group_rows, w.window, w.ring_bytes, w.rhs[1].ptr, w.by_position[1].ptr, dst, nullptr};
   const int threads = w.groups * w.group_rows + 32;
   S35_LAUNCH((k_wave_sweep<true>), 1, threads, w.smem_bytes, s, fwd);
   S35_LAUNCH((k_wave_sweep<false>), 1, threads, w.smem_bytes, s, bwd);
-  if (w.trace.ptr && ++w.trace_calls == 4)
+  if (kWaveTracing && w.trace.ptr && ++w.trace_calls == 4)
     {
       // S35_WAVE_TRACE=<file>: the forward sweep's clocks of the fourth application, one line per tile
       std::vector<long long> h(w.trace.n);
@@ -568,6 +548,12 @@ void wave_launch(DevIlu &p, double *dst, const double *src, cudaStream_t s)
           std::fclose(f);
         }
     }
+}
+
+int env_int(const char *name, int fallback)
+{
+  const char *t = std::getenv(name);
+  return t && *t ? std::atoi(t) : fallback;
 }
 
 // packs both sweeps of the pattern; returns false if the mode does not suit this factor
@@ -590,15 +576,15 @@ bool wave_create(DevIlu &p, const DevMatrix &A, cudaStream_t s)
   DevIlu::Wave &w = p.wave;
   w = DevIlu::Wave();
   opt.slots = kWaveSlots;
-  w.smem_bytes = (size_t)opt.window * 8 + (size_t)opt.ring_bytes + (size_t)kWaveSlots * 16 + 16;
+  w.smem_bytes = (size_t)opt.window * 8 + (size_t)opt.ring_bytes + (size_t)kWaveSlots * 20 + 16;
   if (opt.groups >= kWaveBarriers || opt.groups * opt.group_rows + 32 > kWaveMaxThreads || w.smem_bytes > 227 * 1024)
     return false;
   WavefrontPlan F, B;
   try
     {
-      F = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), true, nullptr, opt);
-      // the backward sweep takes its right-hand sides from the forward sweep's position-ordered result
-      B = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), false, F.position.data(), opt);
+      // the backward sweep first: the forward sweep writes its results straight into the backward sweep's rhs layout
+      B = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), false, nullptr, opt);
+      F = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), true, B.rhs_slot.data(), opt);
     }
   catch (const std::invalid_argument &)
     {
@@ -608,6 +594,7 @@ bool wave_create(DevIlu &p, const DevMatrix &A, cudaStream_t s)
   w.group_rows = opt.group_rows;
   w.window = opt.window;
   w.ring_bytes = opt.ring_bytes;
+  w.rhs_slot.upload(F.rhs_slot, s);
   WavefrontPlan *plans[2] = {&F, &B};
   for (int d = 0; d < 2; ++d)
     {
@@ -620,8 +607,9 @@ bool wave_create(DevIlu &p, const DevMatrix &A, cudaStream_t s)
       w.fresh_fraction[d] = P.entries ? (double)P.fresh_entries / (double)P.entries : 0.0;
       w.blob[d].upload(P.blob, s);
       w.directory[d].upload(P.directory, s);
-      w.desc[d].upload(P.desc, s);
-      w.rhs_index[d].upload(P.rhs_index, s);
+      w.rhs_dir[d].upload(P.rhs_dir, s);
+      w.rhs[d].alloc((size_t)P.rhs_len);
+      w.rhs[d].zero(s);
       w.value_dst[d].upload(P.value_dst, s);
       w.value_src[d].upload(P.value_src, s);
       w.by_position[d].alloc(n);

@@ -42,8 +42,9 @@ struct DevIlu
     size_t smem_bytes = 0;
     int64_t n_values[2] = {0, 0}, stream_bytes[2] = {0, 0};
     DevBuf<unsigned char> blob[2];
-    DevBuf<int32_t> directory[2], desc[2], rhs_index[2], value_dst[2], value_src[2];
-    DevBuf<double> by_position[2];
+    DevBuf<int32_t> directory[2], rhs_dir[2], value_dst[2], value_src[2];
+    DevBuf<int32_t> rhs_slot;        // per row: its place in the forward sweep's rhs layout
+    DevBuf<double> by_position[2], rhs[2]; // rhs: the sweeps' right-hand sides in rhs layout
     DevBuf<long long> trace; // S35_WAVE_TRACE: clocks of the forward sweep's tiles
     int trace_calls = 0;
     double far_fraction[2] = {0., 0.}, fresh_fraction[2] = {0., 0.};

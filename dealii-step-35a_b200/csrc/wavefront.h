@@ -34,16 +34,22 @@
 // of the reading tile, so a concurrently running row may overwrite its slot) are kept out of the chunks, in a list
 // per tile that the owning thread walks ahead of time.
 //
+//  * a global load in a consumer warp stalls it for the load's whole latency at the next shared-memory result it
+//    needs (the loads share scoreboard slots), however far ahead the load was issued: the consumers therefore read
+//    NOTHING from global memory.  The right-hand sides travel through the ring like the factor: they are kept in
+//    "rhs layout" (tile after tile, each tile's rows in order, padded to 128 bytes) and copied in behind the tile.
+//    The forward sweep's input is brought into that layout by a small kernel before the sweep; the forward sweep
+//    writes its results straight into the backward sweep's layout.
+//
 // Packed tile (byte offsets from the tile's start; tile start and size are multiples of 128):
-//   header   16 x int32   [0] first position  [1] rows  [2] warps  [3] n_far
-//                         [4 + w] warp w: (block offset / 128) << 16 | n_pre << 8 | n_chunks
+//   header   16 x int32   [0] first position  [1] rows  [2] warps  [3] n_far  [12] size of the packed tile = offset of
+//                         the right-hand sides in the ring      [4 + w] warp w: (block offset / 128) << 16 | n_pre << 8 | n_chunks
 //   far      n_far x 16 bytes   int32 row in tile, int32 position, double value
 //   warp block (128-byte aligned), for each warp:
-//       backward sweep only: 32 doubles inverse pivots, 32 int32 natural row indices
+//       forward sweep:  32 int32: where the row's result goes in the backward sweep's rhs layout
+//       backward sweep: 32 doubles inverse pivots, 32 int32 natural row indices
 //       n_chunks x { 32 x 4 uint16 slots (byte offsets into the window) | 32 x 2 doubles | 32 x 2 doubles }
-// Beside the stream there are two small arrays the warps look ahead with, without touching the ring:
-//   desc[t] = { rows | (ring offset / 128) << 9, position of the tile's first row }
-//   rhs_index[position] = index of the row's right-hand side in the vector the sweep reads
+// In the ring a tile is followed by its right-hand sides (rows doubles, padded to a multiple of 16).
 #pragma once
 #include <algorithm>
 #include <cmath>
@@ -73,8 +79,9 @@ struct WavefrontPlan
   std::vector<unsigned char> blob;   // all tiles back to back
   std::vector<int32_t> directory;    // per tile: blob offset / 16, ring offset / 16, bytes, tile that must be finished before
                                      // this one may be loaded over it (-1: none)
-  std::vector<int32_t> desc;         // per tile: rows | (ring offset / 128) << 9, first position
-  std::vector<int32_t> rhs_index;    // per position: where the row's right-hand side is read
+  std::vector<int32_t> rhs_dir;      // per tile: offset (in doubles) and size (in bytes) of its right-hand sides in rhs layout
+  std::vector<int32_t> rhs_slot;     // per ROW: where its right-hand side sits in this sweep's rhs layout
+  int32_t rhs_len = 0;               // length of a vector in rhs layout
   std::vector<int32_t> value_dst;    // blob offset / 8 of every factor value in the stream ...
   std::vector<int32_t> value_src;    // ... and its index in the factor's value array
   std::vector<int32_t> position;     // position of every row in this sweep's order
@@ -86,6 +93,7 @@ inline int32_t round_up(int32_t x, int32_t m) { return (x + m - 1) / m * m; }
 
 constexpr int32_t kWaveChunkBytes = 1280;      // one chunk of one warp
 constexpr int32_t kWaveBackwardHead = 384;     // pivots and natural row indices of one warp (backward sweep)
+constexpr int32_t kWaveForwardHead = 128;      // where the rows' results go in the backward sweep's rhs layout
 
 struct WaveFar
 {
@@ -95,9 +103,10 @@ struct WaveFar
 
 // rowptr/col: CSR with ascending columns; diag[r]: position of the diagonal entry of row r.
 // forward: the strictly lower part (unit diagonal); backward: the strictly upper part and the pivot at diag[r].
-// rhs_index: for every row the index of its right-hand side in the vector the sweep reads (nullptr: the row index).
+// next_slot (forward sweep only): for every row, where its result goes in the rhs layout of the sweep that follows
+// (the backward plan's rhs_slot; pack the backward sweep first).
 inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int32_t *col, const int32_t *diag, bool forward,
-                                    const int32_t *rhs_index, const WavefrontOptions &opt)
+                                    const int32_t *next_slot, const WavefrontOptions &opt)
 {
   if (opt.window <= 0 || (opt.window & (opt.window - 1)) != 0 || opt.window > 8192)
     throw std::invalid_argument("wavefront: the window must be a power of two, at most 8192");
@@ -105,7 +114,7 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
     throw std::invalid_argument("wavefront: a warp group is a multiple of 32 threads (at most 256), and there are at least two groups");
   if ((int64_t)opt.group_rows * (opt.groups + 1) > opt.window)
     throw std::invalid_argument("wavefront: the window must hold the rows of groups + 1 tiles"); // fresh values are near
-  if (opt.ring_bytes % 128 != 0 || opt.ring_bytes > 256 * 1024 || opt.max_tile_bytes > opt.ring_bytes / 2 || opt.slots < opt.groups + 1)
+  if (opt.ring_bytes % 128 != 0 || opt.ring_bytes > 256 * 1024 || opt.max_tile_bytes + 8 * opt.group_rows > opt.ring_bytes / 2 || opt.slots < opt.groups + 1)
     throw std::invalid_argument("wavefront: bad ring / tile / slot sizes");
   WavefrontPlan P;
   P.n = n;
@@ -114,7 +123,9 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
   auto first = [&](int32_t r) { return forward ? rowptr[r] : diag[r] + 1; };
   auto last = [&](int32_t r) { return forward ? diag[r] : rowptr[r + 1]; };
   auto len_of = [&](int32_t r) { return last(r) - first(r); };
-  const int32_t warp_head = forward ? 0 : kWaveBackwardHead;
+  const int32_t warp_head = forward ? kWaveForwardHead : kWaveBackwardHead;
+  if (forward && !next_slot && n > 0)
+    throw std::invalid_argument("wavefront: the forward sweep needs the layout of the sweep that reads its result");
 
   // dependency levels
   std::vector<int32_t> level(n, 0);
@@ -212,7 +223,7 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
     tile_begin.push_back(n);
   }
   P.n_tiles = (int32_t)tile_begin.size() - 1;
-  P.rhs_index.assign(n, 0);
+  P.rhs_slot.assign(n, 0);
   std::vector<int32_t> tile_of(n);
   for (int32_t t = 0; t < P.n_tiles; ++t)
     for (int32_t p = tile_begin[t]; p < tile_begin[t + 1]; ++p)
@@ -237,7 +248,7 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
       for (int32_t i = 0; i < rows; ++i)
         {
           const int32_t r = order[p + i];
-          P.rhs_index[p + i] = rhs_index ? rhs_index[r] : r;
+          P.rhs_slot[r] = P.rhs_len + i;
           near[i].clear();
           for (int pass = 0; pass < 2; ++pass) // old entries, then fresh ones; ascending columns in both
             {
@@ -304,6 +315,7 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
       h[1] = rows;
       h[2] = warps;
       h[3] = (int32_t)far.size();
+      h[12] = bytes;
       for (int32_t w = 0; w < 8; ++w)
         h[4 + w] = warp_word[w];
       for (size_t f = 0; f < far.size(); ++f)
@@ -319,7 +331,9 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
           for (int32_t l = 0; l < lanes; ++l)
             {
               const int32_t i = 32 * w + l, r = order[p + i];
-              if (!forward)
+              if (forward)
+                reinterpret_cast<int32_t *>(wb)[l] = next_slot[r];
+              else
                 {
                   reinterpret_cast<int32_t *>(wb + 256)[l] = r;
                   P.value_dst.push_back((int32_t)((blob_begin + warp_at[w] + 8 * l) / 8));
@@ -341,12 +355,16 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
         }
       P.max_tile = std::max(P.max_tile, bytes);
 
-      // place in the ring; the tiles it overwrites must be finished before it may be loaded
-      if (ring_cursor + bytes > opt.ring_bytes)
+      // place tile and right-hand sides in the ring; the tiles they overwrite must be finished before the load
+      const int32_t rhs_bytes = 8 * round_up(rows, 16);
+      if (ring_cursor + bytes + rhs_bytes > opt.ring_bytes)
         ring_cursor = 0;
       ring_begin[t] = ring_cursor;
-      ring_end[t] = ring_cursor + bytes;
-      ring_cursor += bytes;
+      ring_end[t] = ring_cursor + bytes + rhs_bytes;
+      ring_cursor += bytes + rhs_bytes;
+      P.rhs_dir.push_back(P.rhs_len);
+      P.rhs_dir.push_back(rhs_bytes);
+      P.rhs_len += rhs_bytes / 8;
       int32_t need = -1;
       for (int32_t u = oldest_live; u < t; ++u)
         if (ring_begin[u] < ring_end[t] && ring_begin[t] < ring_end[u])
@@ -358,8 +376,6 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
       P.directory.push_back(ring_begin[t] / 16);
       P.directory.push_back(bytes);
       P.directory.push_back(need);
-      P.desc.push_back(rows | ((ring_begin[t] / 128) << 9));
-      P.desc.push_back(p);
     }
   return P;
 }
@@ -377,20 +393,27 @@ inline void wavefront_fill_values(WavefrontPlan &P, const double *lu)
 // is summed as early as the kernel may do it -- when only tiles <= u - groups - 1 are finished; every window slot
 // written by a younger tile is poisoned (NaN) for the duration -- and a tile must not read its own slots.  A wrong
 // `need`, a window slot overwritten too early or an entry classified old too early shows up as a wrong result.
-// by_position should come in as NaN.
-inline void wavefront_apply_host(const WavefrontPlan &P, const double *rhs, double *by_position, double *natural)
+// rhs: the right-hand sides in this plan's rhs layout; by_position should come in as NaN; next_rhs (forward sweep):
+// the vector in the next sweep's rhs layout that receives the results; natural (backward sweep): results by row.
+inline void wavefront_apply_host(const WavefrontPlan &P, const double *rhs, double *by_position, double *natural, double *next_rhs)
 {
   const WavefrontOptions &o = P.opt;
-  const int32_t warp_head = P.forward ? 0 : kWaveBackwardHead;
+  const int32_t warp_head = P.forward ? kWaveForwardHead : kWaveBackwardHead;
   std::vector<double> window(o.window, 0.0);
   std::vector<unsigned char> ring(o.ring_bytes, 0xA5);
   const int G = o.groups;
   std::vector<double> acc_old((size_t)(G + 1) * o.group_rows);
   std::vector<int32_t> first_pos(P.n_tiles + 1, P.n);
-  for (int32_t t = 0; t < P.n_tiles; ++t)
-    first_pos[t] = P.desc[2 * (size_t)t + 1];
+  {
+    int32_t p = 0;
+    for (int32_t t = 0; t < P.n_tiles; ++t)
+      {
+        first_pos[t] = p;
+        p += reinterpret_cast<const int32_t *>(P.blob.data() + (size_t)P.directory[4 * (size_t)t] * 16)[1];
+      }
+  }
   int32_t next_load = 0, next_prepare = 0;
-  auto tile_at = [&](int32_t t) { return ring.data() + (size_t)(P.desc[2 * (size_t)t] >> 9) * 128; };
+  auto tile_at = [&](int32_t t) { return ring.data() + (size_t)P.directory[4 * (size_t)t + 1] * 16; };
   // chunks [c0, c1) of lane l of a warp block added to acc
   auto chunks = [&](const unsigned char *wb, int32_t l, int32_t c0, int32_t c1, double acc, const std::vector<double> &win) {
     for (int32_t c = c0; c < c1; ++c)
@@ -409,10 +432,9 @@ inline void wavefront_apply_host(const WavefrontPlan &P, const double *rhs, doub
   auto progress = [&](int32_t finished) { // tiles < finished are complete
     while (next_load < P.n_tiles && P.directory[4 * (size_t)next_load + 3] < finished)
       {
-        const int32_t *d = P.directory.data() + 4 * (size_t)next_load;
-        if (d[1] * 16 != (P.desc[2 * (size_t)next_load] >> 9) * 128)
-          throw std::logic_error("wavefront: directory and descriptor disagree");
+        const int32_t *d = P.directory.data() + 4 * (size_t)next_load, *rd = P.rhs_dir.data() + 2 * (size_t)next_load;
         std::memcpy(ring.data() + (size_t)d[1] * 16, P.blob.data() + (size_t)d[0] * 16, d[2]);
+        std::memcpy(ring.data() + (size_t)d[1] * 16 + d[2], rhs + rd[0], rd[1]);
         ++next_load;
       }
     while (next_prepare < next_load && next_prepare <= finished + G)
@@ -425,8 +447,8 @@ inline void wavefront_apply_host(const WavefrontPlan &P, const double *rhs, doub
         const unsigned char *T = tile_at(u);
         const int32_t *h = reinterpret_cast<const int32_t *>(T);
         const int32_t rows = h[1], n_far = h[3];
-        if (rows != (P.desc[2 * (size_t)u] & 511) || h[0] != first_pos[u])
-          throw std::logic_error("wavefront: descriptor and tile header disagree");
+        if (h[0] != first_pos[u] || h[12] != P.directory[4 * (size_t)u + 2])
+          throw std::logic_error("wavefront: directory and tile header disagree");
         for (int32_t i = 0; i < rows; ++i)
           {
             const int32_t word = h[4 + i / 32];
@@ -452,6 +474,7 @@ inline void wavefront_apply_host(const WavefrontPlan &P, const double *rhs, doub
       const unsigned char *T = tile_at(t);
       const int32_t *h = reinterpret_cast<const int32_t *>(T);
       const int32_t rows = h[1];
+      const double *tile_rhs = reinterpret_cast<const double *>(T + h[12]);
       // a value of this tile's own slots must not be read by the tile: poison them first
       std::vector<double> win = window;
       for (int32_t i = 0; i < rows; ++i)
@@ -462,20 +485,20 @@ inline void wavefront_apply_host(const WavefrontPlan &P, const double *rhs, doub
           const int32_t word = h[4 + i / 32];
           const unsigned char *wb = T + (size_t)((uint32_t)word >> 16) * 128;
           const double acc = chunks(wb, i % 32, (word >> 8) & 0xff, word & 0xff, acc_old[(size_t)(t % (G + 1)) * o.group_rows + i], win);
-          res[i] = rhs[P.rhs_index[h[0] + i]] - acc;
+          res[i] = tile_rhs[i] - acc;
           if (!P.forward)
             res[i] *= reinterpret_cast<const double *>(wb)[i % 32];
         }
       for (int32_t i = 0; i < rows; ++i)
         {
           const int32_t pos = h[0] + i;
+          const unsigned char *wb = T + (size_t)((uint32_t)h[4 + i / 32] >> 16) * 128;
           window[pos & (o.window - 1)] = res[i];
           by_position[pos] = res[i];
-          if (natural && !P.forward)
-            {
-              const unsigned char *wb = T + (size_t)((uint32_t)h[4 + i / 32] >> 16) * 128;
-              natural[reinterpret_cast<const int32_t *>(wb + 256)[i % 32]] = res[i];
-            }
+          if (P.forward)
+            next_rhs[reinterpret_cast<const int32_t *>(wb)[i % 32]] = res[i];
+          else
+            natural[reinterpret_cast<const int32_t *>(wb + 256)[i % 32]] = res[i];
         }
       progress(t + 1);
     }

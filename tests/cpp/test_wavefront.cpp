@@ -125,15 +125,18 @@ int check(const char *name, const Csr &A, const s35::WavefrontOptions &opt, std:
       x[r] = (y[r] - acc) * A.val[A.diag[r]];
     }
 
-  s35::WavefrontPlan F = s35::wavefront_pack(n, A.rowptr.data(), A.col.data(), A.diag.data(), true, nullptr, opt);
-  // the backward sweep reads its right-hand sides from the forward sweep's position-ordered result
-  s35::WavefrontPlan B = s35::wavefront_pack(n, A.rowptr.data(), A.col.data(), A.diag.data(), false, F.position.data(), opt);
+  // the backward sweep first: the forward sweep writes its results straight into the backward sweep's rhs layout
+  s35::WavefrontPlan B = s35::wavefront_pack(n, A.rowptr.data(), A.col.data(), A.diag.data(), false, nullptr, opt);
+  s35::WavefrontPlan F = s35::wavefront_pack(n, A.rowptr.data(), A.col.data(), A.diag.data(), true, B.rhs_slot.data(), opt);
   s35::wavefront_fill_values(F, A.val.data());
   s35::wavefront_fill_values(B, A.val.data());
   const double junk = std::nan("");
+  std::vector<double> b_layout(F.rhs_len, junk), y_layout(B.rhs_len, junk);
+  for (int32_t r = 0; r < n; ++r)
+    b_layout[F.rhs_slot[r]] = b[r]; // what the permutation kernel does before the forward sweep
   std::vector<double> y_pos(n, junk), x_pos(n, junk), x_nat(n, junk);
-  s35::wavefront_apply_host(F, b.data(), y_pos.data(), nullptr);
-  s35::wavefront_apply_host(B, y_pos.data(), x_pos.data(), x_nat.data());
+  s35::wavefront_apply_host(F, b_layout.data(), y_pos.data(), nullptr, y_layout.data());
+  s35::wavefront_apply_host(B, y_layout.data(), x_pos.data(), x_nat.data(), nullptr);
 
   // the sums are re-associated (old entries first), so the comparison is to rounding, not bit for bit; a schedule
   // error reads a NaN or a stale value and is far outside this bound
@@ -158,9 +161,10 @@ int check(const char *name, const Csr &A, const s35::WavefrontOptions &opt, std:
       for (int32_t t = 0; t < P->n_tiles; ++t)
         {
           const int32_t *d = P->directory.data() + 4 * (size_t)t;
-          const int32_t rows = P->desc[2 * (size_t)t] & 511;
-          if (rows < 1 || rows > opt.group_rows || d[2] > opt.max_tile_bytes || d[2] % 128 || d[0] % 8 || d[1] % 8 ||
-              d[1] * 16 + d[2] > opt.ring_bytes || d[3] >= t || d[3] < t - opt.slots || (P->desc[2 * (size_t)t] >> 9) * 128 != d[1] * 16)
+            const int32_t rows = reinterpret_cast<const int32_t *>(P->blob.data() + (size_t)d[0] * 16)[1];
+          const int32_t *rd = P->rhs_dir.data() + 2 * (size_t)t;
+          if (rows < 1 || rows > opt.group_rows || d[2] > opt.max_tile_bytes || d[2] % 128 || d[0] % 8 || d[1] % 8 || rd[1] % 128 ||
+              rd[0] % 16 || rd[1] < 8 * rows || d[1] * 16 + d[2] + rd[1] > opt.ring_bytes || d[3] >= t || d[3] < t - opt.slots)
             bad |= 8;
         }
       post_max = std::max<int64_t>(post_max, P->max_post_chunks);
@@ -194,7 +198,7 @@ int main()
   tiny_window.groups = 7;
   tiny_tiles.group_rows = 64;
   tiny_tiles.groups = 3;
-  tiny_tiles.max_tile_bytes = 16 * 1024; // one warp, or two with short rows
+  tiny_tiles.max_tile_bytes = 15 * 1024; // one warp, or two with short rows
   tiny_tiles.ring_bytes = 32 * 1024;    // and two or three tiles in the ring: every load waits for an earlier tile
   tiny_tiles.window = 512;
   tiny_tiles.slots = 4;
@@ -245,7 +249,7 @@ int main()
       s35::WavefrontOptions wrong;
       wrong.window = 512; // fewer slots than the rows of groups + 1 tiles (4 x 256)
       const Csr A = grid_pattern(10, 10, 1, 1, identity(100), rng);
-      s35::wavefront_pack(A.n, A.rowptr.data(), A.col.data(), A.diag.data(), true, nullptr, wrong);
+      s35::wavefront_pack(A.n, A.rowptr.data(), A.col.data(), A.diag.data(), false, nullptr, wrong);
       bad |= 16;
     }
   catch (const std::invalid_argument &)

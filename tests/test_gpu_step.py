@@ -7,6 +7,8 @@ field is only defined up to about eps * condition number: on the finer meshes tw
 differ by more than 1e-8 (tests/test_oracle.py shows the two independent CPU restatements differing by
 1e-7 in the pressure on nsbench2 r3, with eps = 1e-8 and with eps = 1e-12 alike).  Those cases carry their
 own, stated, tolerance."""
+import os
+
 import numpy as np
 import pytest
 
@@ -113,6 +115,28 @@ def test_time_steps_match_oracle(pkg, ob, make_disc, mesh, dim, refines, steps, 
     cd_dev = disc.drag_lift(reynolds, u_dev, ctx.get_field(pkg.PRES_N))
     cd_ref = disc.drag_lift(reynolds, u_ref, orc.get_field(pkg.PRES_N))
     assert np.abs(cd_dev - cd_ref).max() <= 1e-6 * max(1.0, np.abs(cd_ref).max())
+
+
+def test_benchmarked_workload_first_step_matches_oracle(pkg, make_disc):
+    """The mesh and refinement bench.py times (cylinderextruded r1, 4.4 M DoF), one step against the oracle built for
+    speed (-O3, OpenMP; the serial -O2 build needs a minute per step here).  The impulsive start is the hardest step of
+    the run (|p| jumps to 1e5, CG takes ~220 iterations); the tolerance is what two correct solvers that stop at
+    eps * ||rhs|| = 1e-8 * ||rhs|| can promise on this mesh, far below a schedule or
+    synchronisation error in the sweeps, which shows up at O(1)."""
+    import oracle_binding as ob_fast
+
+    disc = make_disc("cylinderextruded.s35m", 3, n_global_refines=1, reynolds=100.0, vel_eps=1e-8)
+    ctx = pkg.Ctx(disc.problem)
+    orc = ob_fast.Oracle(disc.problem, fast=True, threads=os.cpu_count() or 1)
+    start_state(pkg, disc, ctx, orc)
+    ctx.advance(2, 1)
+    orc.advance(2, 1)
+    for d in range(3):
+        assert abs(ctx.solver_stats(d).iterations - orc.solver_stats(d).iterations) <= 1
+    assert abs(ctx.solver_stats(-1).iterations - orc.solver_stats(-1).iterations) <= 0.05 * orc.solver_stats(-1).iterations + 1
+    assert_fields_match(pkg, ctx, orc, 3, 5e-7)
+    ctx.close()
+    orc.close()
 
 
 def test_standard_form_and_preconditioner_refresh(pkg, ob, make_disc):

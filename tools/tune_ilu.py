@@ -34,13 +34,8 @@ VARIANT_SETS = {
              + [{"S35_ILU_BACKOFF_NS": str(ns)} for ns in (32, 256)] + [{"S35_ILU_ORDER": "natural"}],
     # wavefront sweeps (one block per sweep): warp groups x rows per group, window, ring; the wide sweep beside them
     "wavefront": [{"S35_ILU_MODE": "wide"}, {}]
-                 + [{"S35_WAVE_GROUPS": str(g), "S35_WAVE_GROUP_ROWS": str(w)} for g, w in ((2, 384), (4, 192), (5, 160), (6, 128))]
-                 + [{"S35_WAVE_RING_KB": "96"}, {"S35_WAVE_WINDOW": "4096", "S35_WAVE_RING_KB": "176"}],
-    # the same on the velocity factors too (long rows)
-    "wavefront_vel": [{"S35_ILU_MODE": "wavefront", "S35_WAVE_TILE_KB": "48", "S35_WAVE_RING_KB": "152"},
-                      {"S35_ILU_MODE": "wavefront", "S35_WAVE_TILE_KB": "48", "S35_WAVE_RING_KB": "152", "S35_WAVE_GROUPS": "3",
-                       "S35_WAVE_GROUP_ROWS": "256"},
-                      {"S35_ILU_MODE": "wavefront", "S35_WAVE_TILE_KB": "40", "S35_WAVE_RING_KB": "96", "S35_WAVE_WINDOW": "16384"}],
+                 + [{"S35_WAVE_GROUPS": str(g), "S35_WAVE_GROUP_ROWS": str(w)} for g, w in ((2, 256), (4, 192), (6, 128))]
+                 + [{"S35_WAVE_RING_KB": "112"}, {"S35_WAVE_WINDOW": "4096", "S35_WAVE_RING_KB": "176"}],
 }
 
 
