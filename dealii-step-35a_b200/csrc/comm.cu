@@ -175,14 +175,17 @@ struct SharedRounds
   }
 };
 
-// S35_DIST_CONCURRENT: 0 / unset = the components take turns on the communicator (default); 1 = a communicator
-// of its own per component (NCCL only; 15-20 % faster per step on 2 and 4 B200s, dead-locked on 8); 2 = the
-// components share the communicator through the collective combiner (protocol tested on the CPU, not yet run
-// on GPUs).
+// How the velocity components of a partitioned run share the communicator (S35_DIST_CONCURRENT):
+//   2 (default)  the component solves run concurrently and hand their collectives to the collective combiner, which
+//                issues them in common rounds on ONE communicator (measured on 2 B200s, r1: 237 ms per step against
+//                335 ms with the components in turn; bit-identical results);
+//   0            the components take turns on the communicator;
+//   1            a communicator of its own per component (NCCL only; dead-locked on 8 GPUs in round 1: kept for the
+//                comparison only).
 int concurrent_mode()
 {
   const char *conc = std::getenv("S35_DIST_CONCURRENT");
-  return conc ? std::atoi(conc) : 0;
+  return conc && *conc ? std::atoi(conc) : 2;
 }
 
 struct NcclComm : Comm

@@ -239,6 +239,9 @@ void Ctx::build(const s35_problem &p)
   if (const char *t = std::getenv("S35_CONCURRENT_COMPONENTS"))
     concurrent_components = concurrent_components && std::atoi(t) != 0;
   S35_CUDA(cudaEventCreateWithFlags(&fork_event, cudaEventDisableTiming));
+  S35_CUDA(cudaStreamCreateWithFlags(&asm_stream, cudaStreamNonBlocking));
+  S35_CUDA(cudaEventCreateWithFlags(&asm_fork, cudaEventDisableTiming));
+  S35_CUDA(cudaEventCreateWithFlags(&asm_done, cudaEventDisableTiming));
   for (int d = 0; d < dim; ++d)
     {
       S35_CUDA(cudaStreamCreateWithFlags(&comp_stream[d], cudaStreamNonBlocking));
@@ -289,6 +292,14 @@ void Ctx::release_handles()
     cudaEventDestroy(e);
   if (fork_event)
     cudaEventDestroy(fork_event);
+  if (asm_fork)
+    cudaEventDestroy(asm_fork);
+  if (asm_done)
+    cudaEventDestroy(asm_done);
+  if (asm_stream)
+    cudaStreamDestroy(asm_stream);
+  asm_fork = asm_done = nullptr;
+  asm_stream = nullptr;
   for (int d = 0; d < 3; ++d)
     {
       if (join_event[d])
@@ -309,8 +320,10 @@ void Ctx::release_handles()
     }
 }
 
-size_t Ctx::begin_section(const char *name)
+size_t Ctx::begin_section(const char *name, cudaStream_t on)
 {
+  if (!on)
+    on = stream;
   if (!timers_enabled)
     return 0;
   auto get_event = [&]() {
@@ -325,16 +338,16 @@ size_t Ctx::begin_section(const char *name)
     return e;
   };
   Pending pd{name, get_event(), get_event()};
-  S35_CUDA(cudaEventRecord(pd.a, stream));
+  S35_CUDA(cudaEventRecord(pd.a, on));
   pending.push_back(pd);
   return pending.size() - 1;
 }
 
-void Ctx::end_section(size_t id)
+void Ctx::end_section(size_t id, cudaStream_t on)
 {
   if (!timers_enabled)
     return;
-  S35_CUDA(cudaEventRecord(pending[id].b, stream));
+  S35_CUDA(cudaEventRecord(pending[id].b, on ? on : stream));
 }
 
 void Ctx::resolve_sections()
@@ -342,6 +355,8 @@ void Ctx::resolve_sections()
   if (pending.empty())
     return;
   S35_CUDA(cudaStreamSynchronize(stream));
+  if (asm_stream)
+    S35_CUDA(cudaStreamSynchronize(asm_stream)); // a section of the assembly task may still be open there
   for (auto &pd : pending)
     {
       float ms = 0.f;
@@ -385,14 +400,39 @@ void Ctx::interpolate_velocity()
   end_section(sec);
 }
 
-// step-35a.cc:1346-1453
-void Ctx::assemble_advection_term()
+// step-35a.cc:1346-1453.  `overlap`: the reference runs this as one of two concurrent tasks (step-35a.cc:1219-1235:
+// assemble_advection_term || projection_step; update_pressure -- they touch disjoint data).  Then the assembly goes to
+// a stream of its own and the caller's stream carries on; whoever reads vel_Advection next calls join_assembly().
+void Ctx::assemble_advection_term(bool overlap)
 {
-  const size_t sec = begin_section("assemble_advection_term");
   const double *us[3] = {u_star[0], u_star[1], u_star[2]};
-  assembler.assemble(vel_adv.val, vel_adv.nnz, us, dt, reynolds, stream);
+  cudaStream_t s = stream;
+  if (overlap && asm_stream)
+    {
+      join_assembly();
+      S35_CUDA(cudaEventRecord(asm_fork, stream)); // u_star is ready
+      S35_CUDA(cudaStreamWaitEvent(asm_stream, asm_fork, 0));
+      s = asm_stream;
+    }
+  const size_t sec = begin_section("assemble_advection_term", s);
+  assembler.assemble(vel_adv.val, vel_adv.nnz, us, dt, reynolds, s);
   vel_adv.values_changed();
-  end_section(sec);
+  end_section(sec, s);
+  if (s == asm_stream)
+    {
+      S35_CUDA(cudaEventRecord(asm_done, asm_stream));
+      asm_in_flight = true;
+    }
+}
+
+// the main stream waits for an assembly that was sent to its own stream
+void Ctx::join_assembly()
+{
+  if (asm_in_flight)
+    {
+      S35_CUDA(cudaStreamWaitEvent(stream, asm_done, 0));
+      asm_in_flight = false;
+    }
 }
 
 // One velocity component of the second half of diffusion_step (step-35a.cc:1308-1324), on stream `s`.
@@ -432,6 +472,7 @@ void Ctx::solve_component(int d, bool reinit_prec, cudaStream_t s)
 void Ctx::diffusion_step(bool reinit_prec)
 {
   cudaStream_t s = stream;
+  join_assembly(); // vel_Advection is read below
   // pres_tmp = -pres_n - 4/3 phi_n + 1/3 phi_n_minus_1
   vec_lincomb3(pres_tmp, DScal(-1.0), pres_n, DScal(-4.0 / 3.0), phi_n, DScal(1.0 / 3.0), phi_nm1, np, s);
   {
@@ -630,7 +671,7 @@ void Ctx::advance(int first_n, int n_steps, int start_n, int start_offset_n, dou
             }
           diffusion_step((n % update_prec == 0) || (n == start_n));
           interpolate_velocity();
-          assemble_advection_term();
+          assemble_advection_term(true); // the reference's task pair: next to projection_step + update_pressure
           projection_step();
           update_pressure();
           resolve_sections();
@@ -638,10 +679,14 @@ void Ctx::advance(int first_n, int n_steps, int start_n, int start_offset_n, dou
     }
   catch (...)
     {
+      asm_in_flight = false;
+      if (asm_stream)
+        cudaStreamSynchronize(asm_stream);
       cudaEventDestroy(e0);
       cudaEventDestroy(e1);
       throw;
     }
+  join_assembly();
   S35_CUDA(cudaEventRecord(e1, stream));
   S35_CUDA(cudaEventSynchronize(e1));
   float ms = 0.f;

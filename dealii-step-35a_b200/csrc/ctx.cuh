@@ -64,6 +64,10 @@ struct Ctx
   ReduceWs ws_comp[3];
   cudaStream_t comp_stream[3] = {nullptr, nullptr, nullptr};
   cudaEvent_t fork_event = nullptr, join_event[3] = {nullptr, nullptr, nullptr};
+  // the assembly task of step-35a.cc:1219-1235 on a stream of its own, next to projection_step + update_pressure
+  cudaStream_t asm_stream = nullptr;
+  cudaEvent_t asm_fork = nullptr, asm_done = nullptr;
+  bool asm_in_flight = false;
   bool concurrent_components = true;
   CgSolver cg;
   AdvectionAssembler assembler;
@@ -96,7 +100,8 @@ struct Ctx
   Ctx &operator=(const Ctx &) = delete;
 
   void interpolate_velocity();
-  void assemble_advection_term();
+  void assemble_advection_term(bool overlap = false);
+  void join_assembly();
   void diffusion_step(bool reinit_prec);
   void solve_component(int d, bool reinit_prec, cudaStream_t s);
   void projection_step();
@@ -105,8 +110,8 @@ struct Ctx
 
   double *field(s35_field f, int component, int64_t &len);
 
-  size_t begin_section(const char *name);
-  void end_section(size_t id);
+  size_t begin_section(const char *name, cudaStream_t on = nullptr);
+  void end_section(size_t id, cudaStream_t on = nullptr);
   void resolve_sections();
 };
 

@@ -96,17 +96,16 @@ def test_partitioned_time_steps_match_the_single_gpu_run(pkg, make_disc, mesh, d
     assert rel_diff(p, p1) < 5e-6 and rel_diff(phi, phi1) < 5e-6
 
 
-@pytest.mark.skipif(os.environ.get("S35_TEST_COMBINER") != "1",
-                    reason="the collective combiner on the device has not been run yet (set S35_TEST_COMBINER=1)")
 @pytest.mark.parametrize("mesh,dim,refines,n_ranks,steps", [("nsbench2.s35m", 2, 1, 2, 4), ("cylinder3d.s35m", 3, 0, 3, 2)])
 def test_components_sharing_the_communicator_through_the_combiner(pkg, make_disc, monkeypatch, mesh, dim, refines, n_ranks, steps):
-    """S35_DIST_CONCURRENT=2: the velocity components of every rank run concurrently and hand their collectives to
-    the combiner (csrc/combiner.h).  Concurrency must not change a single bit: same operations, same operands,
-    reductions in rank order."""
+    """The default of a partitioned run (S35_DIST_CONCURRENT=2): the velocity components of every rank run concurrently
+    and hand their collectives to the combiner (csrc/combiner.h).  Against the components taking turns
+    (S35_DIST_CONCURRENT=0), concurrency must not change a single bit: same operations, same operands, reductions in
+    rank order."""
     disc = make_disc(mesh, dim, n_global_refines=refines, vel_eps=1e-11)
-    monkeypatch.delenv("S35_DIST_CONCURRENT", raising=False)
+    monkeypatch.setenv("S35_DIST_CONCURRENT", "0")
     u0, p0, phi0, its0 = run_partitioned(pkg, disc, n_ranks, steps)
-    monkeypatch.setenv("S35_DIST_CONCURRENT", "2")
+    monkeypatch.delenv("S35_DIST_CONCURRENT", raising=False)
     u1, p1, phi1, its1 = run_partitioned(pkg, disc, n_ranks, steps)
     assert its0 == its1
     for a, b in zip(u0 + [p0, phi0], u1 + [p1, phi1]):
