@@ -168,6 +168,8 @@ _SIGNATURES = [
     ("s35_part_initial_pressure", c_double_p, [_VP]),
     ("s35_disc_partition_cells", C.c_int, [_VP, C.c_int32, c_int32_p]),
     ("s35_mesh_convert", C.c_int, [C.c_char_p, C.c_int32, C.c_char_p]),
+    ("s35_mesh_h5_save", C.c_int, [C.c_char_p, C.c_char_p, c_double_p, C.c_int64]),
+    ("s35_mesh_h5_load", C.c_int, [C.c_char_p, C.c_char_p, c_double_p, C.c_int64, C.POINTER(C.c_int64)]),
     ("s35_sim_create", C.c_int, [C.POINTER(Params), C.c_char_p, C.c_int32, C.POINTER(_VP)]),
     ("s35_sim_destroy", None, [_VP]),
     ("s35_sim_run", C.c_int, [_VP, C.c_int32, C.c_int32]),
@@ -671,6 +673,20 @@ def vec_add_and_dot(a, x, y, w):
     r = C.c_double()
     check(lib().s35_vec_add_and_dot(x.size, a, dptr(x), dptr(y), dptr(w), C.byref(r)))
     return y, r.value
+
+
+def h5_save(file_name, dataset_name, values):
+    """H5::save of the reference's h5.h: one 1-D double dataset, added to the file if it exists"""
+    v = f64(values)
+    check_host(host_lib().s35_mesh_h5_save(file_name.encode(), dataset_name.encode(), dptr(v), v.size))
+
+
+def h5_load(file_name, dataset_name):
+    n = C.c_int64()
+    check_host(host_lib().s35_mesh_h5_load(file_name.encode(), dataset_name.encode(), None, 0, C.byref(n)))
+    out = np.zeros(n.value)
+    check_host(host_lib().s35_mesh_h5_load(file_name.encode(), dataset_name.encode(), dptr(out), n.value, C.byref(n)))
+    return out
 
 
 def mesh_convert(in_file, dim, out_file):

@@ -2,6 +2,7 @@
 #include "../../include/step35a_host.h"
 #include "navier_stokes_projection.h"
 #include "partition.h"
+#include "h5.h"
 
 #include <chrono>
 #include <cstring>
@@ -286,6 +287,27 @@ s35_status s35_mesh_convert(const char *in_file, int32_t dim, const char *out_fi
         throw std::runtime_error("mesh_convert: unknown output extension");
     },
     S35_ERR_IO);
+}
+
+s35_status s35_mesh_h5_save(const char *file_name, const char *dataset_name, const double *values, int64_t n)
+{
+  return guarded([&] {
+    if (!file_name || !dataset_name || n < 0 || (n > 0 && !values))
+      throw std::invalid_argument("h5 save: null argument or negative length");
+    H5::save(file_name, dataset_name, std::vector<double>(values, values + n));
+  });
+}
+
+s35_status s35_mesh_h5_load(const char *file_name, const char *dataset_name, double *values, int64_t capacity, int64_t *n)
+{
+  return guarded([&] {
+    if (!file_name || !dataset_name || !n || capacity < 0 || (capacity > 0 && !values))
+      throw std::invalid_argument("h5 load: null argument or negative capacity");
+    std::vector<double> v;
+    H5::load(file_name, dataset_name, v);
+    *n = (int64_t)v.size();
+    std::copy(v.begin(), v.begin() + std::min<int64_t>(capacity, *n), values);
+  });
 }
 
 #ifndef S35_HOST_ONLY

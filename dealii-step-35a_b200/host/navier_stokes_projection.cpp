@@ -1,10 +1,11 @@
 #include "navier_stokes_projection.h"
 
-#include "h5lite.h"
+#include "h5.h"
 
 #include <chrono>
 #include <cstdlib>
 #include <cstdio>
+#include <fstream>
 #include <iomanip>
 #include <iostream>
 #include <sstream>
@@ -144,9 +145,10 @@ void NavierStokesProjection<dim>::save_checkpoint()
 {
   if (save_checkpoint_file_name.empty())
     return;
-  const std::string file = output_directory + "/" + save_checkpoint_file_name;
+  // the file name as given, like the reference (step-35a.cc:891) and like load_checkpoint(): a run restarted with the
+  // same name finds the file
+  const std::string &file = save_checkpoint_file_name;
   std::cout << "outfile name is '" << save_checkpoint_file_name << "'" << std::endl;
-  std::remove(file.c_str());
   std::vector<double> values;
   for (const CheckpointEntry &e : checkpoint_entries(dim))
     {
@@ -269,29 +271,88 @@ void NavierStokesProjection<dim>::assemble_advection_term()
   check(s35_assemble_advection_term(ctx));
 }
 
-// The reference writes mesh.h5 / solution-%09d.h5 / solution.xdmf through deal.II's DataOut and a
-// snapshot-%09d.h5 of u_n (step-35a.cc:1548-1661).  Here the fields go into solution-%09d.h5 and
-// snapshot-%09d.h5 in the container of h5lite.h, datasets "v0".."v{dim-1}", "p" and "a0".."a{dim-1}".
+// step-35a.cc:1548-1661.  The reference hands the fields to deal.II's DataOut, which writes mesh.h5 (once),
+// solution-%09d.h5 and solution.xdmf, and saves u_n as snapshot-%09d.h5 with H5::save_block_vector.  Here the same
+// files are written by hand as real HDF5 (h5min.h): mesh.h5 holds /nodes (vertices x 3) and /cells (cells x 2^dim,
+// vertex indices in XDMF order), solution-*.h5 the vertex values /v0 ... /v{dim-1} and /p, solution.xdmf one grid per
+// output step that points into them, snapshot-*.h5 the blocks /a0 ... /a{dim-1} of u_n.
 template <int dim>
 void NavierStokesProjection<dim>::output_results(const unsigned int step, const double time)
 {
-  (void)time;
   char name[64];
   std::snprintf(name, sizeof(name), "solution-%09u.h5", step);
-  const std::string sol = output_directory + "/" + name;
+  const std::string sol_name = name, sol = output_directory + "/" + sol_name;
   std::snprintf(name, sizeof(name), "snapshot-%09u.h5", step);
   const std::string snap = output_directory + "/" + name;
-  std::remove(sol.c_str());
-  std::remove(snap.c_str());
-  std::vector<double> v(disc->vel.n_dofs), p(disc->pres.n_dofs);
-  for (int d = 0; d < dim; ++d)
+  const int vpc = 1 << dim, dpc = dim == 2 ? 9 : 27;
+  const size_t n_vertices = disc->mesh.vertices.size() / dim, n_cells = (size_t)disc->mesh.n_cells();
+  if (write_mesh)
     {
-      check(s35_ctx_get_field(ctx, S35_U_N, d, v.data()));
-      H5::save(sol, "v" + std::to_string(d), v);
-      H5::save(snap, "a" + std::to_string(d), v);
+      write_mesh = false;
+      h5min::File mesh;
+      h5min::Dataset &nodes = mesh["nodes"], &cells = mesh["cells"];
+      nodes.dims = {n_vertices, 3};
+      nodes.data.assign(3 * n_vertices, 0.0);
+      for (size_t v = 0; v < n_vertices; ++v)
+        for (int k = 0; k < dim; ++k)
+          nodes.data[3 * v + k] = disc->mesh.vertices[v * dim + k];
+      // lexicographic vertex order -> the order XDMF wants for Quadrilateral / Hexahedron
+      const int xdmf_order[8] = {0, 1, 3, 2, 4, 5, 7, 6};
+      cells.dims = {n_cells, (uint64_t)vpc};
+      cells.data.resize(n_cells * vpc);
+      for (size_t c = 0; c < n_cells; ++c)
+        for (int v = 0; v < vpc; ++v)
+          cells.data[c * vpc + v] = (double)disc->mesh.cells[c * vpc + xdmf_order[v]];
+      h5min::write_file(output_directory + "/mesh.h5", mesh);
+      std::ofstream(output_directory + "/finite_element.txt") << "FE_Q<" << dim << ">(" << deg + 1 << ")" << std::endl;
     }
+  // vertex values: a Q2 cell holds its vertices at the corners of the 3^dim lexicographic lattice, a Q1 cell in order
+  std::vector<std::vector<double>> blocks(dim, std::vector<double>(disc->vel.n_dofs));
+  std::vector<double> p(disc->pres.n_dofs);
+  for (int d = 0; d < dim; ++d)
+    check(s35_ctx_get_field(ctx, S35_U_N, d, blocks[d].data()));
   check(s35_ctx_get_field(ctx, S35_PRES_N, 0, p.data()));
-  H5::save(sol, "p", p);
+  h5min::File solution;
+  for (int d = 0; d <= dim; ++d)
+    {
+      h5min::Dataset &set = solution[d < dim ? "v" + std::to_string(d) : std::string("p")];
+      set.dims = {n_vertices};
+      set.data.assign(n_vertices, 0.0);
+      for (size_t c = 0; c < n_cells; ++c)
+        for (int v = 0; v < vpc; ++v)
+          {
+            const int corner = (v & 1) * 2 + ((v >> 1) & 1) * 6 + ((v >> 2) & 1) * 18;
+            const size_t vertex = (size_t)disc->mesh.cells[c * vpc + v];
+            set.data[vertex] = d < dim ? blocks[d][disc->vel.cell_dofs[c * dpc + corner]] : p[disc->pres.cell_dofs[c * vpc + v]];
+          }
+    }
+  h5min::write_file(sol, solution);
+  H5::save_block_vector(snap, blocks);
+  // solution.xdmf: rewritten with one more grid at every output step, like DataOut::write_xdmf_file
+  {
+    std::ostringstream e;
+    e << "      <Grid Name=\"mesh\" GridType=\"Uniform\">\n        <Time Value=\"" << time << "\"/>\n"
+      << "        <Geometry GeometryType=\"XYZ\">\n          <DataItem Dimensions=\"" << n_vertices
+      << " 3\" NumberType=\"Float\" Precision=\"8\" Format=\"HDF\">mesh.h5:/nodes</DataItem>\n        </Geometry>\n"
+      << "        <Topology TopologyType=\"" << (dim == 2 ? "Quadrilateral" : "Hexahedron") << "\" NumberOfElements=\"" << n_cells
+      << "\">\n          <DataItem Dimensions=\"" << n_cells << " " << vpc
+      << "\" NumberType=\"Float\" Precision=\"8\" Format=\"HDF\">mesh.h5:/cells</DataItem>\n        </Topology>\n";
+    for (int d = 0; d <= dim; ++d)
+      {
+        const std::string field = d < dim ? "v" + std::to_string(d) : std::string("p");
+        e << "        <Attribute Name=\"" << field << "\" AttributeType=\"Scalar\" Center=\"Node\">\n          <DataItem Dimensions=\""
+          << n_vertices << "\" NumberType=\"Float\" Precision=\"8\" Format=\"HDF\">" << sol_name << ":/" << field
+          << "</DataItem>\n        </Attribute>\n";
+      }
+    e << "      </Grid>\n";
+    xdmf_entries.push_back(e.str());
+    std::ofstream x(output_directory + "/solution.xdmf");
+    x << "<?xml version=\"1.0\" ?>\n<!DOCTYPE Xdmf SYSTEM \"Xdmf.dtd\" []>\n<Xdmf Version=\"2.0\">\n  <Domain>\n"
+      << "    <Grid Name=\"CellTime\" GridType=\"Collection\" CollectionType=\"Temporal\">\n";
+    for (const std::string &g : xdmf_entries)
+      x << g;
+    x << "    </Grid>\n  </Domain>\n</Xdmf>\n";
+  }
 }
 
 // TimerOutput summary (step-35a.cc:508,714): device time per section

@@ -53,6 +53,8 @@ protected:
   s35_ctx *ctx = nullptr;
 
   double height = 0, width = 0;
+  bool write_mesh = true;                  // step-35a.cc: mesh.h5 is written with the first output only
+  std::vector<std::string> xdmf_entries;   // one grid per output step (step-35a.cc:1652-1656)
 
   void create_triangulation_and_dofs(const unsigned int n_refines, const std::string &mesh_file);
   void initialize();

@@ -82,6 +82,13 @@ s35_status s35_disc_partition_cells(const s35_disc *d, int32_t n_ranks, int32_t 
 /* mesh file conversion (tools/pack_meshes.py and the reader round-trip tests) */
 s35_status s35_mesh_convert(const char *in_file, int32_t dim, const char *out_file);
 
+/* ---- h5.h: H5::save / H5::load (reference h5.h:66-121) ----
+ * One 1-D dataset of doubles in a real HDF5 file (written by hand, host/h5min.h: libhdf5 is not needed).  save adds
+ * the dataset to an existing file or creates the file; load reads at most `capacity` values into `values` and reports
+ * the dataset's length in *n (call with capacity 0 to ask for the length). */
+s35_status s35_mesh_h5_save(const char *file_name, const char *dataset_name, const double *values, int64_t n);
+s35_status s35_mesh_h5_load(const char *file_name, const char *dataset_name, double *values, int64_t capacity, int64_t *n);
+
 /* ---- the driver: NavierStokesProjection<dim> ---- */
 typedef struct s35_sim s35_sim;
 

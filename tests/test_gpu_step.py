@@ -188,6 +188,7 @@ def test_simulation_driver_runs_like_the_reference_loop(pkg, ob, make_disc, tmp_
     import os
     from conftest import MESH_DIR, run_params
     params = run_params(pkg, n_global_refines=1, final_time=0.005)
+    params.save_checkpoint_file_name = str(tmp_path / "checkpoint_save.h5").encode()
     sim = pkg.Simulation(params, os.path.join(MESH_DIR, "nsbench2.s35m"), 2)
     assert sim.n_steps == 9  # (T - t0)/dt = 10, steps n = 2..10
     cwd = os.getcwd()
@@ -200,9 +201,37 @@ def test_simulation_driver_runs_like_the_reference_loop(pkg, ob, make_disc, tmp_
     start_state(pkg, sim.disc, orc)
     orc.advance(2, 9)
     assert_fields_match(pkg, sim.ctx, orc, 2, 1e-7)
-    assert os.path.exists(tmp_path / "solution-000000001.h5")
     ms, calls = sim.ctx.section_ms("projection_step_solve")
     assert calls == 9 and ms > 0
+    # the files of output_results and save_checkpoint (step-35a.cc:879-900, 1623-1660) are real HDF5: read them with
+    # the independent reader of test_h5.py
+    from test_h5 import parse_hdf5
+    mesh = parse_hdf5(str(tmp_path / "mesh.h5"))
+    verts, cells, _, _ = sim.disc.mesh()
+    assert mesh["nodes"].shape == (len(verts), 3) and np.array_equal(mesh["nodes"][:, :2], verts)
+    assert mesh["cells"].shape == (len(cells), 4) and np.array_equal(mesh["cells"], cells[:, [0, 1, 3, 2]])
+    sol = parse_hdf5(str(tmp_path / "solution-000000001.h5"))
+    assert sorted(sol) == ["p", "v0", "v1"] and all(len(v) == len(verts) for v in sol.values())
+    assert np.array_equal(sol["p"], 25.0 - verts[:, 0])          # written before the first step: the initial pressure
+    snap = parse_hdf5(str(tmp_path / "snapshot-000000001.h5"))
+    assert sorted(snap) == ["a0", "a1"] and len(snap["a0"]) == sim.disc.nv
+    xdmf = open(tmp_path / "solution.xdmf").read()
+    assert "mesh.h5:/nodes" in xdmf and "solution-000000001.h5:/v1" in xdmf and 'TopologyType="Quadrilateral"' in xdmf
+    ck = parse_hdf5(str(tmp_path / "checkpoint_save.h5"))
+    assert sorted(ck) == sorted(["u_n0", "u_n1", "u_n_minus_10", "u_n_minus_11", "phi_n", "phi_n_minus_1", "pres_n", "pres_n_minus_1"])
+    for name, field, d in (("u_n0", pkg.U_N, 0), ("u_n_minus_11", pkg.U_N_MINUS_1, 1), ("phi_n", pkg.PHI_N, 0), ("pres_n_minus_1", pkg.PRES_N_MINUS_1, 0)):
+        assert ck[name].tobytes() == sim.ctx.get_field(field, d).tobytes()
+    # a restart picks the state up bit for bit (load_checkpoint, step-35a.cc:856-876)
+    params2 = run_params(pkg, n_global_refines=1, final_time=0.01)
+    params2.initial_time = 0.005
+    params2.load_checkpoint_file_name = str(tmp_path / "checkpoint_save.h5").encode()
+    sim2 = pkg.Simulation(params2, os.path.join(MESH_DIR, "nsbench2.s35m"), 2)
+    os.chdir(tmp_path)
+    try:
+        sim2.run(verbose=False, output_interval=999)
+    finally:
+        os.chdir(cwd)
+    assert np.isfinite(sim2.ctx.get_field(pkg.PRES_N)).all()
 
 
 GOLDEN_TOL = {"nsbench2_r0_steps8.npz": 1e-8, "nsbench2_r1_steps5.npz": 5e-8, "cylinder3d_r0_steps2.npz": 1e-8,
