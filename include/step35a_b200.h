@@ -137,7 +137,10 @@ s35_status s35_vec_add_and_dot(int64_t n, double a, const double *x, double *y, 
  *   - The first call on each device looks up the device address of that array; make that first call before
  *     starting any stream capture.
  *   - All calls share the one array: two calls that can run on the GPU at the same time (different streams
- *     without an ordering between them) race and give wrong results.  Calls on one stream are safe. */
+ *     without an ordering between them) race and give wrong results.  Calls on one stream are safe.
+ *   - The looked-up address is remembered per device for the life of the process: after a cudaDeviceReset() it is
+ *     stale, and this entry point must not be used again in that process.
+ *   - n == 0 stores 0.0 in *result_device and reads neither x nor y (they may be NULL). */
 s35_status s35_vec_dot_device_noalloc(int64_t n, const double *x_device, const double *y_device, double *result_device,
                                       void *stream);
 

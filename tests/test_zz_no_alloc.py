@@ -19,13 +19,14 @@ pytestmark = pytest.mark.gpu
 MAX_N = 2097152  # stated limit of the built-in scratch array (include/step35a_b200.h)
 
 
-def device_dot(pkg, torch, x_host, y_host):
+def device_dot(pkg, torch, x_host, y_host, stream=None):
     x = torch.from_numpy(np.ascontiguousarray(x_host)).cuda()
     y = torch.from_numpy(np.ascontiguousarray(y_host)).cuda()
     out = torch.full((1,), float("nan"), dtype=torch.float64, device="cuda")
     torch.cuda.synchronize()
     status = pkg.lib().s35_vec_dot_device_noalloc(x.numel(), C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr()),
-                                                  C.c_void_p(out.data_ptr()), None)
+                                                  C.c_void_p(out.data_ptr()),
+                                                  C.c_void_p(stream.cuda_stream) if stream is not None else None)
     pkg.check(status)
     torch.cuda.synchronize()
     return float(out.cpu()[0])
@@ -57,3 +58,18 @@ def test_sizes_beyond_the_scratch_array_are_rejected(pkg):
     # the largest admissible length still works
     x, y = seeded_vector(MAX_N, 1), seeded_vector(MAX_N, 2)
     assert device_dot(pkg, torch, x, y) == pkg.vec_dot(x, y)
+
+
+def test_empty_vectors_and_a_stream_of_the_callers(pkg):
+    torch = pytest.importorskip("torch")
+    # n == 0: the result is 0.0 and the vectors are not touched (null pointers are fine)
+    out = torch.full((1,), float("nan"), dtype=torch.float64, device="cuda")
+    torch.cuda.synchronize()
+    pkg.check(pkg.lib().s35_vec_dot_device_noalloc(0, None, None, C.c_void_p(out.data_ptr()), None))
+    torch.cuda.synchronize()
+    assert float(out.cpu()[0]) == 0.0
+    # a non-default stream owned by the caller, twice in a row on that stream
+    stream = torch.cuda.Stream()
+    for n, seed in ((50001, 3), (777, 4)):
+        x, y = seeded_vector(n, seed), seeded_vector(n, seed + 50)
+        assert device_dot(pkg, torch, x, y, stream) == pkg.vec_dot(x, y)
