@@ -1,6 +1,8 @@
 #include "krylov.cuh"
 
+#include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <limits>
 
 namespace s35 {
@@ -159,6 +161,55 @@ bool GmresSolver::solve(const DevMatrix &P, const double *values, DevIlu &prec, 
   return state == SolverState::success;
 }
 
+namespace {
+
+// before the loop graph: tolerance and iteration limit where the device-side check reads them
+__global__ void k_cg_arm(double *sc, double tol, double max_iterations)
+{
+  sc[6] = tol;
+  sc[7] = max_iterations;
+  sc[8] = 0.0; // iterations done
+  sc[9] = 0.0; // SolverControl state: 0 iterate, 1 success, 2 failure
+}
+
+// SolverControl::check (solver_check above) after the residual update of an iteration, and the WHILE condition
+__global__ void k_cg_check(double *sc, cudaGraphConditionalHandle loop)
+{
+  const double it = sc[8] + 1.0, res = sc[3];
+  sc[8] = it;
+  unsigned int go_on = 1;
+  if (res <= sc[6])
+    {
+      sc[9] = 1.0;
+      go_on = 0;
+    }
+  else if (it >= sc[7] || res != res)
+    {
+      sc[9] = 2.0;
+      go_on = 0;
+    }
+  cudaGraphSetConditional(loop, go_on);
+}
+
+bool cg_graph_enabled()
+{
+  const char *t = std::getenv("S35_CG_GRAPH");
+  return !(t && std::atoi(t) == 0);
+}
+
+} // namespace
+
+CgSolver::~CgSolver()
+{
+  for (LoopGraph &l : loops)
+    {
+      if (l.exec)
+        cudaGraphExecDestroy(l.exec);
+      if (l.graph)
+        cudaGraphDestroy(l.graph);
+    }
+}
+
 void CgSolver::init(int32_t n_owned, int32_t n_local_, cudaStream_t s)
 {
   n = n_owned;
@@ -169,8 +220,9 @@ void CgSolver::init(int32_t n_owned, int32_t n_local_, cudaStream_t s)
   g.zero(s);
   d.zero(s);
   h.zero(s);
-  scal.alloc(8);
-  res_host.alloc(2);
+  scal.alloc(16);
+  scal.zero(s);
+  res_host.alloc(4);
   ws.init(s);
   stream = s;
 }
@@ -224,6 +276,73 @@ bool CgSolver::solve(const DevMatrix &P, const double *values, DevIlu *prec, dou
       precondition(h, g);
       vec_lincomb(d, DScal(-1.0), h, DScal(0.0), nullptr, n, s);
       dot(sc + GH, g, h);
+      if (!dist.comm && cg_graph_enabled())
+        {
+          // the whole loop as one graph launch (krylov.cuh); one graph per combination of operands
+          const void *key[6] = {P.rowptr.ptr, values, prec, x, b, inv_diag};
+          LoopGraph *loop = nullptr;
+          for (LoopGraph &l : loops)
+            if (std::equal(key, key + 6, l.key))
+              loop = &l;
+          if (!loop)
+            {
+              if (loops.size() >= 8) // a caller that keeps changing its operands: forget the oldest graph
+                {
+                  cudaGraphExecDestroy(loops.front().exec);
+                  cudaGraphDestroy(loops.front().graph);
+                  loops.erase(loops.begin());
+                }
+              loops.emplace_back();
+              loop = &loops.back();
+              std::copy(key, key + 6, loop->key);
+              S35_CUDA(cudaGraphCreate(&loop->graph, 0));
+              cudaGraphConditionalHandle handle;
+              S35_CUDA(cudaGraphConditionalHandleCreate(&handle, loop->graph, 1, cudaGraphCondAssignDefault));
+              cudaGraphNodeParams params = {};
+              params.type = cudaGraphNodeTypeConditional;
+              params.conditional.handle = handle;
+              params.conditional.type = cudaGraphCondTypeWhile;
+              params.conditional.size = 1;
+              cudaGraphNode_t node;
+              S35_CUDA(cudaGraphAddNode(&node, loop->graph, nullptr, 0, &params));
+              cudaGraph_t body = params.conditional.phGraph_out[0];
+              const int64_t launches_before = g_launch_count.load();
+              S35_CUDA(cudaStreamBeginCaptureToGraph(s, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+              try
+                {
+                  // one iteration; after the check the rest only touches h, d and the scalars, so running it once more
+                  // after the stopping iteration (the loop ends at the END of a body) leaves x and g as the reference has them
+                  matvec(d, h);
+                  dot(sc + DH, d, h);
+                  scalar_divide(sc + ALPHA, sc + GH, sc + DH, nullptr, s);
+                  vec_cg_update(sc + RES, x, g, DScal(sc + ALPHA), d, h, n, kSqrt, ws, s);
+                  S35_LAUNCH(k_cg_check, 1, 1, 0, s, sc, handle);
+                  precondition(h, g);
+                  dot(sc + GHNEW, g, h);
+                  scalar_divide(sc + BETA, sc + GHNEW, sc + GH, sc + GH, s);
+                  vec_lincomb(d, DScal(sc + BETA), d, DScal(-1.0), h, n, s);
+                }
+              catch (...)
+                {
+                  cudaGraph_t dummy = nullptr;
+                  cudaStreamEndCapture(s, &dummy);
+                  throw;
+                }
+              S35_CUDA(cudaStreamEndCapture(s, nullptr));
+              loop->launches_per_iteration = g_launch_count.load() - launches_before;
+              g_launch_count.fetch_sub(loop->launches_per_iteration); // recorded, not run
+              S35_CUDA(cudaGraphInstantiate(&loop->exec, loop->graph, 0));
+            }
+          S35_LAUNCH(k_cg_arm, 1, 1, 0, s, sc, tol, (double)max_iterations);
+          S35_CUDA(cudaGraphLaunch(loop->exec, s));
+          S35_CUDA(cudaMemcpyAsync(res_host.ptr, sc + RES, sizeof(double), cudaMemcpyDeviceToHost, s));
+          S35_CUDA(cudaMemcpyAsync(res_host.ptr + 1, sc + 8, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+          S35_CUDA(cudaStreamSynchronize(s));
+          res = res_host.ptr[0];
+          it = (int)res_host.ptr[1];
+          state = res_host.ptr[2] == 1.0 ? SolverState::success : SolverState::failure;
+          g_launch_count.fetch_add((int64_t)it * loop->launches_per_iteration);
+        }
       while (state == SolverState::iterate)
         {
           ++it;

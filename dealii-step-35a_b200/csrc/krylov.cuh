@@ -13,6 +13,8 @@
 #include "ilu.cuh"
 #include "vecops.cuh"
 
+#include <vector>
+
 namespace s35 {
 
 // SolverControl::check
@@ -80,11 +82,25 @@ struct CgSolver
 {
   int32_t n = 0, n_local = 0;
   DevBuf<double> g, d, h;
-  DevBuf<double> scal;    // [0] d.h  [1] alpha  [2] gh  [3] res  [4] gh_new  [5] beta
+  DevBuf<double> scal;    // [0] d.h  [1] alpha  [2] gh  [3] res  [4] gh_new  [5] beta  [6] tol  [7] max its  [8] it  [9] state
   PinnedBuf<double> res_host;
   ReduceWs ws;
   cudaStream_t stream = 0;
   DistLink dist;
+
+  // Single GPU: the iteration runs as ONE graph launch -- a WHILE node (CUDA conditional graph node) whose body is one
+  // CG iteration and whose condition a one-thread kernel sets from SolverControl::check on the device -- so that no
+  // iteration waits for the host.  The iterates and the stopping iteration are those of the host-driven loop.  One
+  // graph per (matrix, preconditioner, x, b) combination is kept.  S35_CG_GRAPH=0 switches back to the host loop.
+  struct LoopGraph
+  {
+    const void *key[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    int64_t launches_per_iteration = 0;
+  };
+  std::vector<LoopGraph> loops;
+  ~CgSolver();
 
   void init(int32_t n_owned, int32_t n_local, cudaStream_t s);
   // prec may be null; then inv_diag (Jacobi, h = inv_diag .* g) is used if given, else PreconditionIdentity
