@@ -557,7 +557,7 @@ int env_int(const char *name, int fallback)
 }
 
 // packs both sweeps of the pattern; returns false if the mode does not suit this factor
-bool wave_create(DevIlu &p, const DevMatrix &A, cudaStream_t s)
+bool wave_create(DevIlu &p, const DevMatrix &A, cudaStream_t s, bool force = false)
 {
   const int32_t n = A.n_rows;
   if (n == 0)
@@ -590,6 +590,8 @@ bool wave_create(DevIlu &p, const DevMatrix &A, cudaStream_t s)
     {
       return false; // e.g. a row that does not fit a tile: the wide sweep takes this factor
     }
+  if (!force && (double)(F.far_entries + B.far_entries) > 0.02 * (double)(F.entries + B.entries + 1))
+    return false; // too many values outside the window: every one is a trip to L2 in the middle of a tile
   w.groups = opt.groups;
   w.group_rows = opt.group_rows;
   w.window = opt.window;
@@ -732,14 +734,23 @@ void DevIlu::create(const DevMatrix &A, cudaStream_t s)
   if (const char *g = std::getenv("S35_ILU_BACKOFF_NS"))
     backoff_ns = std::max(0, std::min(10000, std::atoi(g)));
   factored = false;
-  // Which sweep: the wavefront mode (one block, levels handed over inside an SM) wins where the levels are narrow and
-  // the rows short; S35_ILU_MODE = wide | wavefront overrides the choice, S35_WAVE_MAX_ROW moves the row-length bound.
+  // Which sweep.  The wavefront mode (one block, levels handed over inside an SM) wins where the levels are narrow
+  // and the sweep's values stay in its shared-memory window: factors with short rows (the Q1 pressure matrices:
+  // 2.13 -> 1.27 ms per application at r1), and factors with long rows whose bandwidth is below half the window (the
+  // Q2 velocity matrices of the coarse meshes: cylinder3d r0 21.5 -> 16.0 ms per diffusion step).  On the large
+  // velocity factors a sixth of the values has left the window and one SM cannot stream 600 MB per sweep: they keep
+  // the wide sweep.  S35_ILU_MODE = wide | wavefront overrides the choice, S35_WAVE_MAX_ROW moves the row-length bound.
   wave = Wave();
   const char *mode = std::getenv("S35_ILU_MODE");
   const bool force_wide = mode && std::strcmp(mode, "wide") == 0, force_wave = mode && std::strcmp(mode, "wavefront") == 0;
   const double mean_row = n ? (double)A.nnz / n : 0.0;
-  if (!force_wide && (force_wave || mean_row <= (double)env_int("S35_WAVE_MAX_ROW", 40)))
-    wave_create(*this, A, s);
+  int32_t bandwidth = 0;
+  for (int32_t r = 0; r < n; ++r)
+    if (rp[r + 1] > rp[r])
+      bandwidth = std::max(bandwidth, std::max(r - cl[rp[r]], cl[rp[r + 1] - 1] - r));
+  const bool suits = mean_row <= (double)env_int("S35_WAVE_MAX_ROW", 40) || bandwidth <= env_int("S35_WAVE_WINDOW", 8192) / 2;
+  if (!force_wide && (force_wave || suits))
+    wave_create(*this, A, s, force_wave);
 }
 
 void DevIlu::factor(const double *values, double strengthen_diagonal, cudaStream_t s)
