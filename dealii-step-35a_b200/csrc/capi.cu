@@ -431,6 +431,17 @@ s35_status s35_ctx_get_operator_values(s35_ctx *ctx, s35_operator op, int32_t co
         S35_REQUIRE(component >= 0 && component < c.dim, "component out of range");
         // with ilu_blocks > 1 or on a partition the factor lives on a filtered pattern (fewer entries, other positions):
         // there is no value array on the caller's pattern to hand out
+        if (c.off_diagonals > 0)
+          { // the factor's entries at the matrix's own positions; the added side diagonals have no place in the caller's array
+            std::vector<double> wide(c.vel_blk.nnz);
+            S35_CUDA(cudaMemcpyAsync(wide.data(), c.prec_vel[component].lu, wide.size() * sizeof(double), cudaMemcpyDeviceToHost,
+                                     c.stream));
+            S35_CUDA(cudaStreamSynchronize(c.stream));
+            for (size_t i = 0; i < wide.size(); ++i)
+              if (c.vel_wide_src[i] >= 0)
+                values[c.vel_wide_src[i]] = wide[i];
+            return;
+          }
         if (c.use_blocks)
           throw Error(S35_ERR_UNSUPPORTED, "the ILU factor of a block / partitioned preconditioner is not on the matrix pattern");
         src = c.prec_vel[component].lu;

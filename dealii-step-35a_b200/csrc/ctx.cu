@@ -73,9 +73,11 @@ void Ctx::build(const s35_problem &p)
                 "problem: null or negative-length inflow constraint lists");
   S35_REQUIRE(p.dt > 0 && p.reynolds > 0, "problem: dt and Reynolds must be positive");
   S35_REQUIRE(p.vel_max_iterations >= 1 && p.vel_update_prec >= 1, "problem: bad solver parameters");
-  if (p.vel_off_diagonals != 0)
-    throw Error(S35_ERR_UNSUPPORTED, "off_diagonals > 0 (banded ILU pattern augmentation) is not part of this build; "
-                                     "use off_diagonals = 0 as parameter-file.prm does");
+  S35_REQUIRE(p.vel_off_diagonals >= 0, "problem: off_diagonals must not be negative");
+  if (p.vel_off_diagonals > 0 && (p.ilu_blocks > 1 || (p.dist && p.dist->n_ranks > 1)))
+    throw Error(S35_ERR_UNSUPPORTED, "off_diagonals > 0 (widened ILU pattern) together with ilu_blocks > 1 or a partition "
+                                     "is not part of this build");
+  off_diagonals = p.vel_off_diagonals;
   dim = p.dim;
   n_cells = p.n_cells;
   nv = p.n_vel;
@@ -213,12 +215,51 @@ void Ctx::build(const s35_problem &p)
     blk.create(n_own, n_own, rp.data(), cl.data(), nullptr, s);
     src.upload(from, s);
   };
+  // off_diagonals = k > 0 (SparseILU::AdditionalData::extra_off_diagonals, step-35a.cc:1070-1074 and 1312-1319): the
+  // factor's pattern is the matrix's plus the entries (r, r - k .. r + k); an added entry starts at 0 (source -1)
+  // and takes fill-in.  The same filtered-pattern plumbing as the blocks carries it.
+  auto make_widened = [&](const DevMatrix &A, DevMatrix &wide, DevBuf<int32_t> &src) {
+    const int32_t n = A.n_rows, k = off_diagonals;
+    std::vector<int32_t> rp(n + 1, 0), cl, from;
+    for (int32_t r = 0; r < n; ++r)
+      {
+        int32_t pos = A.h_rowptr[r];
+        const int32_t end = A.h_rowptr[r + 1];
+        auto copy_below = [&](int32_t limit) {
+          for (; pos < end && A.h_col[pos] < limit; ++pos)
+            {
+              cl.push_back(A.h_col[pos]);
+              from.push_back(pos);
+            }
+        };
+        for (int32_t c = std::max(0, r - k); c <= std::min(n - 1, r + k); ++c)
+          {
+            copy_below(c);
+            const bool present = pos < end && A.h_col[pos] == c;
+            cl.push_back(c);
+            from.push_back(present ? pos++ : -1);
+          }
+        copy_below(n);
+        rp[r + 1] = (int32_t)cl.size();
+      }
+    wide.create(n, n, rp.data(), cl.data(), nullptr, s);
+    src.upload(from, s);
+    return from;
+  };
   const bool use_halo = D != nullptr && (nv_own < nv || np_own < np);
-  use_blocks = use_halo || ilu_blocks > 1;
+  use_blocks = use_halo || ilu_blocks > 1 || off_diagonals > 0;
   if (use_blocks)
     {
-      make_block(vel_adv, nv_own, vel_blk, vel_blk_src);
-      make_block(plap, np_own, plap_blk, plap_blk_src);
+      if (off_diagonals > 0)
+        {
+          vel_wide_src = make_widened(vel_adv, vel_blk, vel_blk_src);
+          make_widened(plap, plap_blk, plap_blk_src);
+        }
+      else
+        {
+          make_block(vel_adv, nv_own, vel_blk, vel_blk_src);
+          make_block(plap, np_own, plap_blk, plap_blk_src);
+        }
       for (int d = 0; d < dim; ++d)
         blk_val[d].alloc(vel_blk.nnz);
       gather_values(plap_blk.val, plap.val, plap_blk_src, plap_blk.nnz, s);

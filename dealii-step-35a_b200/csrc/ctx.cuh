@@ -44,8 +44,10 @@ struct Ctx
   DistLink vel_link, pres_link;
   HaloDev comp_halo[3];           // per velocity component: its own send buffer and communicator
   DistLink comp_link[3];
-  bool use_blocks = false;        // the ILU(0) factors live on a filtered pattern (partition and / or ilu_blocks)
+  bool use_blocks = false;        // the ILU(0) factors live on a pattern of their own (partition, ilu_blocks, off_diagonals)
   int32_t ilu_blocks = 1;
+  int32_t off_diagonals = 0;      // > 0: the filtered pattern is the matrix's widened by that many side diagonals
+  std::vector<int32_t> vel_wide_src; // host copy of vel_blk_src in that mode (s35_ctx_get_operator_values)
   DevMatrix vel_blk, plap_blk;
   DevBuf<int32_t> vel_blk_src, plap_blk_src;
   DevBuf<double> blk_val[3];

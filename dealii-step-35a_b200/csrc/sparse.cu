@@ -157,7 +157,10 @@ __global__ void k_gather(double *__restrict__ dst, const double *__restrict__ sr
 {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
-    dst[i] = src[perm[i]];
+    {
+      const int32_t from = perm[i]; // < 0: an entry the source pattern does not have (widened ILU pattern)
+      dst[i] = from >= 0 ? src[from] : 0.0;
+    }
 }
 
 int pick_lanes(int64_t nnz, int32_t n_rows)

@@ -38,7 +38,7 @@ typedef enum s35_status
   S35_ERR_CUDA = 2,           /* CUDA runtime error, or no device */
   S35_ERR_NO_CONVERGENCE = 3, /* SolverControl::NoConvergence */
   S35_ERR_ZERO_PIVOT = 4,     /* SparseILU: zero pivot */
-  S35_ERR_UNSUPPORTED = 5,    /* parameter combination outside this build (e.g. off_diagonals > 0) */
+  S35_ERR_UNSUPPORTED = 5,    /* parameter combination outside this build (e.g. off_diagonals > 0 on a partition) */
   S35_ERR_IO = 6
 } s35_status;
 

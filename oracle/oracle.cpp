@@ -176,6 +176,55 @@ void ilu0_apply(const Csr &P, const double *lu, const double *src, double *dst)
     }
 }
 
+// SparseLUDecomposition with AdditionalData::extra_off_diagonals = k [A.3]: the factor's pattern is the matrix's pattern
+// plus the k sub- and super-diagonals next to the main diagonal (entries (r, r - k .. r + k) inside the matrix).
+// source[i]: where entry i of the new pattern sits in the matrix's value array, -1 for an added entry (value 0).
+void augment_pattern(const Csr &P, int k, Csr &out, std::vector<int> &source)
+{
+  const int n = P.n_rows;
+  std::vector<int> rp(n + 1, 0), cl;
+  source.clear();
+  for (int r = 0; r < n; ++r)
+    {
+      int pos = P.rowptr[r];
+      const int end = P.rowptr[r + 1];
+      auto flush_below = [&](int c_limit) { // matrix entries with column < c_limit
+        while (pos < end && P.col[pos] < c_limit)
+          {
+            cl.push_back(P.col[pos]);
+            source.push_back(pos);
+            ++pos;
+          }
+      };
+      for (int c = std::max(0, r - k); c <= std::min(n - 1, r + k); ++c)
+        {
+          flush_below(c);
+          if (pos < end && P.col[pos] == c)
+            {
+              cl.push_back(c);
+              source.push_back(pos);
+              ++pos;
+            }
+          else
+            {
+              cl.push_back(c);
+              source.push_back(-1);
+            }
+        }
+      flush_below(n);
+      rp[r + 1] = (int)cl.size();
+    }
+  out.set(n, n, rp.data(), cl.data());
+}
+
+// the matrix's values on the factor's pattern
+void gather_on_pattern(const std::vector<int> &source, const double *a, std::vector<double> &out)
+{
+  out.resize(source.size());
+  for (size_t i = 0; i < source.size(); ++i)
+    out[i] = source[i] >= 0 ? a[source[i]] : 0.0;
+}
+
 // SolverControl::check
 enum State
 {
@@ -194,7 +243,7 @@ State check(int step, double value, double tol, int max_steps)
 
 // SolverGMRES<Vector<double>>::solve, left preconditioning, default residual [A.1]
 bool gmres(const Csr &P, const double *A, const double *lu, double *x, const double *b, double tol, int max_its,
-           int n_tmp_vectors, s35_solver_stats &stats)
+           int n_tmp_vectors, s35_solver_stats &stats, const Csr *factor_pattern = nullptr)
 {
   const int n = P.n_rows;
   if (n_tmp_vectors < 3)
@@ -216,7 +265,7 @@ bool gmres(const Csr &P, const double *A, const double *lu, double *x, const dou
       vmult(P, A, x, p.data(), false);
       for (int i = 0; i < n; ++i)
         p[i] = -1. * p[i] + 1. * b[i]; // p.sadd(-1., 1., b)
-      ilu0_apply(P, lu, p.data(), v.data());
+      ilu0_apply(factor_pattern ? *factor_pattern : P, lu, p.data(), v.data());
       double rho = l2_norm(v.data(), n);
       if (accumulated == 0)
         stats.initial_residual = rho;
@@ -232,7 +281,7 @@ bool gmres(const Csr &P, const double *A, const double *lu, double *x, const dou
           ++accumulated;
           Vec &vv = tmp[inner + 1];
           vmult(P, A, tmp[inner].data(), p.data(), false);
-          ilu0_apply(P, lu, p.data(), vv.data());
+          ilu0_apply(factor_pattern ? *factor_pattern : P, lu, p.data(), vv.data());
           dim = inner + 1;
           // modified_gram_schmidt
           double norm_vv_start = 0;
@@ -306,13 +355,13 @@ bool gmres(const Csr &P, const double *A, const double *lu, double *x, const dou
 
 // SolverCG<Vector<double>>::solve [A.2]; lu == nullptr: PreconditionIdentity, inv_diag: Jacobi
 bool cg(const Csr &P, const double *A, const double *lu, double *x, const double *b, double tol, int max_its,
-        s35_solver_stats &stats, const double *inv_diag = nullptr)
+        s35_solver_stats &stats, const double *inv_diag = nullptr, const Csr *factor_pattern = nullptr)
 {
   const int n = P.n_rows;
   Vec g(n), d(n), h(n);
   auto precondition = [&](double *dst, const double *src) {
     if (lu)
-      ilu0_apply(P, lu, src, dst);
+      ilu0_apply(factor_pattern ? *factor_pattern : P, lu, src, dst);
     else if (inv_diag)
       for (int i = 0; i < n; ++i)
         dst[i] = inv_diag[i] * src[i];
@@ -496,6 +545,10 @@ struct oracle_ctx
   int dim = 0, n_cells = 0, nv = 0, np = 0;
   double dt = 0, Re = 0, eps = 0, diag_strength = 0;
   int ilu_blocks = 1;
+  // off_diagonals > 0 (ref:1070-1074, 1312-1319): the factors live on patterns widened by that many side diagonals
+  int off_diagonals = 0;
+  Csr velc_ilu, plap_ilu;
+  std::vector<int> velc_ilu_src, plap_ilu_src;
   int max_its = 0, krylov = 0, update_prec = 0;
   bool rotational = true;
   FE *fe = nullptr;
@@ -780,8 +833,8 @@ const char *oracle_last_error(void) { return g_error.c_str(); }
 int oracle_create(const s35_problem *p, oracle_ctx **out)
 {
   return guarded([&] {
-    if (p->vel_off_diagonals != 0)
-      throw std::runtime_error("oracle: off_diagonals > 0 is not restated");
+    if (p->vel_off_diagonals < 0 || (p->vel_off_diagonals > 0 && p->ilu_blocks > 1))
+      throw std::runtime_error("oracle: off_diagonals < 0, or off_diagonals together with ilu_blocks");
     oracle_ctx *c = new oracle_ctx;
     c->dim = p->dim;
     c->n_cells = p->n_cells;
@@ -792,6 +845,7 @@ int oracle_create(const s35_problem *p, oracle_ctx **out)
     c->eps = p->vel_eps;
     c->diag_strength = p->vel_diag_strength;
     c->ilu_blocks = std::max(1, (int)p->ilu_blocks);
+    c->off_diagonals = p->vel_off_diagonals;
     c->max_its = p->vel_max_iterations;
     c->krylov = p->vel_krylov_size;
     c->update_prec = p->vel_update_prec;
@@ -804,6 +858,11 @@ int oracle_create(const s35_problem *p, oracle_ctx **out)
     c->velm.set(c->nv, c->nv, p->velm_rowptr, p->velm_col);
     c->grad.set(c->nv, c->np, p->grad_rowptr, p->grad_col);
     c->plap.set(c->np, c->np, p->plap_rowptr, p->plap_col);
+    if (c->off_diagonals > 0)
+      {
+        augment_pattern(c->velc, c->off_diagonals, c->velc_ilu, c->velc_ilu_src);
+        augment_pattern(c->plap, c->off_diagonals, c->plap_ilu, c->plap_ilu_src);
+      }
     c->pmass.set(c->np, c->np, p->pmass_rowptr, p->pmass_col);
     c->vel_mass.assign(p->velm_val, p->velm_val + c->velm.nnz());
     c->pres_laplace.assign(p->plap_val, p->plap_val + c->plap.nnz());
@@ -823,15 +882,25 @@ int oracle_create(const s35_problem *p, oracle_ctx **out)
         c->flow_dofs[d].assign(p->flow_dofs[d], p->flow_dofs[d] + p->n_flow[d]);
         c->flow_vals[d].assign(p->flow_vals[d], p->flow_vals[d] + p->n_flow[d]);
         c->vel_it[d].assign(c->velc.nnz(), 0.);
-        c->prec_vel[d].assign(c->velc.nnz(), 0.);
+        c->prec_vel[d].assign(c->off_diagonals > 0 ? c->velc_ilu.nnz() : c->velc.nnz(), 0.);
         for (Vec *v : {&c->u_n[d], &c->u_nm1[d], &c->u_star[d], &c->force[d], &c->v_tmp[d]})
           v->assign(c->nv, 0.);
       }
     for (Vec *v : {&c->pres_n, &c->pres_nm1, &c->phi_n, &c->phi_nm1, &c->pres_tmp})
       v->assign(c->np, 0.);
     // pressure preconditioners are built once (ref:1070-1075)
-    c->prec_pres.resize(c->plap.nnz());
-    ilu0_factor(c->plap, c->pres_laplace.data(), c->diag_strength, c->prec_pres.data(), c->ilu_blocks);
+    if (c->off_diagonals > 0)
+      {
+        Vec widened;
+        gather_on_pattern(c->plap_ilu_src, c->pres_laplace.data(), widened);
+        c->prec_pres.resize(c->plap_ilu.nnz());
+        ilu0_factor(c->plap_ilu, widened.data(), c->diag_strength, c->prec_pres.data());
+      }
+    else
+      {
+        c->prec_pres.resize(c->plap.nnz());
+        ilu0_factor(c->plap, c->pres_laplace.data(), c->diag_strength, c->prec_pres.data(), c->ilu_blocks);
+      }
     build_mass_cholesky(*c);
     std::memset(c->stats_vel, 0, sizeof(c->stats_vel));
     c->stats_proj = c->stats_mass = s35_solver_stats{0, 0., 0., 0.};
@@ -859,6 +928,13 @@ int oracle_get_operator_values(oracle_ctx *c, int op, int comp, double *values)
 {
   return guarded([&] {
     const Vec *v = op == S35_VEL_ADVECTION ? &c->vel_advection : op == S35_VEL_IT_MATRIX ? &c->vel_it[comp] : &c->prec_vel[comp];
+    if (op == S35_VEL_ILU && c->off_diagonals > 0)
+      { // the factor's entries at the matrix's own positions; the added side diagonals have no place in the caller's array
+        for (size_t i = 0; i < c->velc_ilu_src.size(); ++i)
+          if (c->velc_ilu_src[i] >= 0)
+            values[c->velc_ilu_src[i]] = (*v)[i];
+        return;
+      }
     std::copy(v->begin(), v->end(), values);
   });
 }
@@ -953,12 +1029,18 @@ int oracle_diffusion_step(oracle_ctx *c, int reinit_prec)
           try
             {
               condense(c->velc, c->vel_it[d].data(), c->force[d].data(), c->flow_dofs[d], c->flow_vals[d]);
-              if (reinit_prec)
+              if (reinit_prec && c->off_diagonals > 0)
+                {
+                  Vec widened;
+                  gather_on_pattern(c->velc_ilu_src, c->vel_it[d].data(), widened);
+                  ilu0_factor(c->velc_ilu, widened.data(), c->diag_strength, c->prec_vel[d].data());
+                }
+              else if (reinit_prec)
                 ilu0_factor(c->velc, c->vel_it[d].data(), c->diag_strength, c->prec_vel[d].data(), c->ilu_blocks);
               // diffusion_component_solve (ref:1330-1338)
               const double tol = c->eps * l2_norm(c->force[d].data(), nv);
               const bool ok = gmres(c->velc, c->vel_it[d].data(), c->prec_vel[d].data(), c->u_n[d].data(), c->force[d].data(),
-                                    tol, c->max_its, c->krylov, c->stats_vel[d]);
+                                    tol, c->max_its, c->krylov, c->stats_vel[d], c->off_diagonals > 0 ? &c->velc_ilu : nullptr);
               if (!ok)
                 throw std::runtime_error("GMRES: no convergence");
               for (size_t i = 0; i < c->flow_dofs[d].size(); ++i)
@@ -995,7 +1077,7 @@ int oracle_projection_step(oracle_ctx *c)
       for (int i : c->proj)
         c->pres_tmp[i] = 0.;
       const bool ok = cg(c->plap, c->pres_laplace.data(), c->prec_pres.data(), c->phi_n.data(), c->pres_tmp.data(), tol,
-                         c->max_its, c->stats_proj);
+                         c->max_its, c->stats_proj, nullptr, c->off_diagonals > 0 ? &c->plap_ilu : nullptr);
       if (!ok)
         throw std::runtime_error("CG: no convergence");
       for (int i : c->proj)

@@ -177,11 +177,42 @@ def test_no_convergence_is_reported(pkg, make_disc):
     assert e.value.status == 3
 
 
-def test_unsupported_off_diagonals(pkg, make_disc):
+@pytest.mark.parametrize("mesh,dim,refines,k,reynolds", [("nsbench2.s35m", 2, 1, 5, 100.0), ("nsbench2.s35m", 2, 0, 60, 100.0),
+                                                        ("cylinder3d.s35m", 3, 0, 3, 20.0)])
+def test_off_diagonals_widen_the_ilu_pattern(pkg, ob, make_disc, mesh, dim, refines, k, reynolds):
+    """off_diagonals = k > 0 (step-35a.cc:1070-1074, 1312-1319; 5 is the Readme's example, 60 the declared default):
+    both ILU factors live on the matrix pattern plus k side diagonals.  Factor entries, iteration counts and fields
+    against the oracle, and fewer velocity iterations than with the plain pattern."""
+    disc = make_disc(mesh, dim, n_global_refines=refines, reynolds=reynolds, vel_off_diagonals=k)
+    ctx, orc = make_pair(pkg, ob, disc)
+    nnz = int(disc.csr("velc")[0][-1])
+    ctx.advance(2, 1)
+    orc.advance(2, 1)
+    for d in range(dim):
+        l_dev, l_ref = ctx.get_operator_values(pkg.VEL_ILU, nnz, d), orc.get_operator_values(pkg.VEL_ILU, nnz, d)
+        assert rel_diff(l_dev, l_ref) < 1e-11
+    ctx.advance(3, 4)
+    orc.advance(3, 4)
+    for d in range(dim):
+        assert abs(ctx.solver_stats(d).iterations - orc.solver_stats(d).iterations) <= 1
+    assert abs(ctx.solver_stats(-1).iterations - orc.solver_stats(-1).iterations) <= 1
+    assert_fields_match(pkg, ctx, orc, dim, 1e-7 if refines else TOL)
+    plain = ob.Oracle(make_disc(mesh, dim, n_global_refines=refines, reynolds=reynolds).problem)
+    start_state(pkg, disc, plain)
+    plain.advance(2, 5)
+    assert ctx.solver_stats(-1).iterations <= plain.solver_stats(-1).iterations
+    assert sum(ctx.solver_stats(d).iterations for d in range(dim)) <= sum(plain.solver_stats(d).iterations for d in range(dim))
+
+
+def test_off_diagonals_with_blocks_or_negative_are_rejected(pkg, make_disc):
     disc = make_disc("nsbench2.s35m", 2, vel_off_diagonals=5)
     with pytest.raises(pkg.S35Error) as e:
-        pkg.Ctx(disc.problem)
+        pkg.Ctx(pkg.with_ilu_blocks(disc.problem, 2))
     assert e.value.status == 5
+    disc = make_disc("nsbench2.s35m", 2, vel_off_diagonals=-1)
+    with pytest.raises(pkg.S35Error) as e:
+        pkg.Ctx(disc.problem)
+    assert e.value.status == 1
 
 
 def test_simulation_driver_runs_like_the_reference_loop(pkg, ob, make_disc, tmp_path):

@@ -329,6 +329,38 @@ def test_block_ilu_alternative_in_the_oracle(pkg, ob, make_disc):
     assert runs[1][1] >= runs[0][1]
 
 
+def test_off_diagonals_widen_the_factor_pattern_in_the_oracle(pkg, ob, make_disc):
+    """off_diagonals = k (SparseILU::AdditionalData::extra_off_diagonals, step-35a.cc:1070-1074, 1312-1319): the factor is
+    the ILU(0) of the matrix on its pattern plus the entries (r, r - k .. r + k).  The widened pattern is rebuilt here with
+    scipy, independently of the oracle's own construction; fewer iterations than with the plain pattern."""
+    k = 5
+    disc = make_disc("nsbench2.s35m", 2, n_global_refines=1, vel_off_diagonals=k)
+    plain_disc = make_disc("nsbench2.s35m", 2, n_global_refines=1)
+    orc, plain = ob.Oracle(disc.problem), ob.Oracle(plain_disc.problem)
+    start_state(pkg, disc, orc, plain)
+    orc.advance(2, 1)       # the first step factorises its own matrix: VEL_IT_MATRIX and VEL_ILU belong together
+    plain.advance(2, 1)
+    rp, cl, _ = disc.csr("velc")
+    n, nnz = disc.nv, int(rp[-1])
+    rows = np.repeat(np.arange(n), np.diff(rp))
+    band = sp.diags([np.ones(n - abs(o)) for o in range(-k, k + 1)], list(range(-k, k + 1)), format="csr")
+    mark = (sp.csr_matrix((np.ones(nnz), cl, rp), shape=(n, n)) + band).tocsr()   # structural union, all entries > 0
+    mark.sort_indices()
+    assert mark.nnz > nnz
+    for d in range(2):
+        a = orc.get_operator_values(pkg.VEL_IT_MATRIX, nnz, d)
+        A = sp.csr_matrix((a, cl, rp), shape=(n, n))
+        values = np.asarray(A[np.repeat(np.arange(n), np.diff(mark.indptr)), mark.indices]).ravel()
+        lu = ob.ilu0_factor(n, mark.indptr.astype(np.int32), mark.indices.astype(np.int32), values, 0.0)
+        at_matrix_positions = np.asarray(sp.csr_matrix((lu, mark.indices, mark.indptr), shape=(n, n))[rows, cl]).ravel()
+        assert rel_diff(orc.get_operator_values(pkg.VEL_ILU, nnz, d), at_matrix_positions) < 1e-13
+    orc.advance(3, 2)
+    plain.advance(3, 2)
+    for d in range(2):
+        assert orc.solver_stats(d).iterations <= plain.solver_stats(d).iterations
+    assert orc.solver_stats(-1).iterations < plain.solver_stats(-1).iterations
+
+
 @pytest.mark.parametrize("reynolds,rotational", [(100.0, 1), (10.0, 1), (100.0, 0)])
 def test_known_answer_poiseuille_flow_is_a_fixed_point(pkg, ob, tmp_path, reynolds, rotational):
     """Analytic known answer (the reference ships none): plane Poiseuille flow solves the Navier-Stokes equations with
