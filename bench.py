@@ -55,6 +55,8 @@ def parse_args():
     ap.add_argument("--parity-steps", type=int, default=0, help="steps compared with the oracle (default: 3 on one GPU, 2 on several)")
     ap.add_argument("--ilu-blocks", type=int, default=1,
                     help="GATED ALTERNATIVE (not the reference's preconditioner): ILU(0) of k index-range blocks")
+    ap.add_argument("--off-diagonals", type=int, default=0,
+                    help="off_diagonals of parameter-file.prm (0 there and here; the reference's Readme reports 5 as faster)")
     ap.add_argument("--deadline", type=int, default=600, help="abort the whole run after this many seconds")
     return ap.parse_args()
 
@@ -120,7 +122,7 @@ def workload_name(args):
 
 def build_disc(pkg, args):
     params = pkg.default_params(reynolds=REYNOLDS.get(args.mesh, 100.0), final_time=1.0, dt=5e-4, vel_eps=1e-8,
-                                vel_off_diagonals=0, vel_diag_strength=0.0, vel_update_prec=100, vel_krylov_size=30,
+                                vel_off_diagonals=args.off_diagonals, vel_diag_strength=0.0, vel_update_prec=100, vel_krylov_size=30,
                                 vel_max_iterations=1000, n_global_refines=args.refines, pressure_degree=1, rotational=1)
     mesh_file = os.path.join(ROOT, "meshes", args.mesh + ".s35m")
     return pkg.Disc(mesh_file, args.dim, params), params
@@ -132,6 +134,8 @@ def preconditioner_label(args, world):
     if world > 1:
         return ("block-local ILU(0) per rank (couplings to ghost DoFs dropped; NOT the reference's global SparseILU: "
                 "iteration counts differ from the single-GPU run)")
+    if args.off_diagonals > 0:
+        return "ILU(0) on the pattern widened by off_diagonals = %d, as the reference's SparseILU with that setting" % args.off_diagonals
     return "ILU(0) as the reference's SparseILU"
 
 

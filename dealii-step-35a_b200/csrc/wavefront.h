@@ -240,6 +240,11 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
   std::vector<int32_t> n_old(opt.group_rows);
   std::vector<WaveFar> far;
   std::vector<int32_t> far_k;
+  constexpr int32_t kMaxPlaces = 4 * 255;
+  std::vector<std::vector<int32_t>> place_of(opt.group_rows);              // per row of the tile: place of entry j
+  std::vector<char> placed((size_t)(opt.group_rows + 32) * kMaxPlaces, 0); // per row and place: taken by a real entry
+  std::vector<int32_t> bank_load((size_t)kMaxPlaces * 16);                 // per place and bank pair: different values so far
+  std::vector<std::vector<int32_t>> place_slots(kMaxPlaces);
   for (int32_t t = 0; t < P.n_tiles; ++t)
     {
       const int32_t p = tile_begin[t], tile_end = tile_begin[t + 1], rows = tile_end - p, warps = (rows + 31) / 32;
@@ -297,6 +302,55 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
           warp_at[w] = cursor;
           warp_word[w] = ((cursor / 128) << 16) | (n_pre << 8) | (n_pre + n_post);
           cursor = round_up(cursor + warp_head + kWaveChunkBytes * (n_pre + n_post), 128);
+          // Where a row's entries sit in its chunks.  The 16 lanes of a half-warp read the window together, one place at
+          // a time; two different values in the same pair of banks cost an extra trip.  Old entries may take any place
+          // of the first n_pre chunks, fresh ones any place of the chunks after them: lane by lane, entry by entry, the
+          // free place with the fewest clashes so far.  (The order of a row's sum is the order of its places: fixed here.)
+          if (4 * (n_pre + n_post) > kMaxPlaces)
+            throw std::invalid_argument("wavefront: a row has too many chunks");
+          for (int32_t half = 0; half < 2; ++half)
+            {
+              std::fill(bank_load.begin(), bank_load.end(), 0);
+              for (auto &v : place_slots)
+                v.clear();
+              for (int32_t l = 16 * half; l < std::min(lanes, 16 * half + 16); ++l)
+                {
+                  const int32_t i = 32 * w + l;
+                  place_of[i].assign(near[i].size(), -1);
+                  std::fill(placed.begin() + (size_t)i * kMaxPlaces, placed.begin() + (size_t)(i + 1) * kMaxPlaces, (char)0);
+                  for (size_t j = 0; j < near[i].size(); ++j)
+                    {
+                      const bool old = (int32_t)j < n_old[i];
+                      const int32_t lo = old ? 0 : 4 * n_pre, hi = old ? 4 * n_pre : 4 * (n_pre + n_post);
+                      const int32_t slot = near[i][j].slot, bank = (slot / 8) % 16;
+                      int32_t best = -1, best_cost = 1 << 30;
+                      for (int32_t place = lo; place < hi; ++place)
+                        {
+                          if (placed[(size_t)i * kMaxPlaces + place])
+                            continue;
+                          const auto &seen = place_slots[place];
+                          const int32_t cost = std::find(seen.begin(), seen.end(), slot) != seen.end() ? 0 : bank_load[place * 16 + bank];
+                          if (cost < best_cost)
+                            {
+                              best_cost = cost;
+                              best = place;
+                            }
+                        }
+                      if (best < 0)
+                        throw std::logic_error("wavefront: no place left for an entry");
+                      place_of[i][j] = best;
+                      placed[(size_t)i * kMaxPlaces + best] = 1;
+                      auto &seen = place_slots[best];
+                      if (std::find(seen.begin(), seen.end(), slot) == seen.end())
+                        {
+                          seen.push_back(slot);
+                          ++bank_load[best * 16 + bank];
+                        }
+                    }
+                }
+            }
+          for (int32_t l = lanes; l < 32; ++l) // lanes without a row: nothing placed
+            std::fill(placed.begin() + (size_t)(32 * w + l) * kMaxPlaces, placed.begin() + (size_t)(32 * w + l + 1) * kMaxPlaces, (char)0);
           P.post_chunks += n_post;
           P.max_post_chunks = std::max(P.max_post_chunks, n_post);
           P.stored_entries += (int64_t)128 * (n_pre + n_post);
@@ -342,8 +396,7 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
               const int32_t n_pre = (warp_word[w] >> 8) & 0xff;
               for (size_t j = 0; j < near[i].size(); ++j)
                 {
-                  // old entry j sits at place j, fresh entry j at place 4 n_pre + (j - n_old)
-                  const int32_t place = (int32_t)j < n_old[i] ? (int32_t)j : 4 * n_pre + (int32_t)j - n_old[i];
+                  const int32_t place = place_of[i][j];
                   const int32_t c = place / 4, u = place % 4;
                   unsigned char *cb = wb + warp_head + kWaveChunkBytes * c;
                   reinterpret_cast<uint16_t *>(cb)[4 * l + u] = (uint16_t)near[i][j].slot;
@@ -351,7 +404,24 @@ inline WavefrontPlan wavefront_pack(int32_t n, const int32_t *rowptr, const int3
                   P.value_dst.push_back((int32_t)((blob_begin + o_val) / 8));
                   P.value_src.push_back(near[i][j].k);
                 }
+              (void)n_pre;
             }
+          // a padding entry (value 0.0) reads what a real entry at the same place of its half-warp reads: a broadcast,
+          // no extra trip through the banks; where the half-warp has no real entry there, all its lanes read slot 0
+          const int32_t n_places = 4 * (warp_word[w] & 0xff);
+          for (int32_t half = 0; half < 2; ++half)
+            for (int32_t place = 0; place < n_places; ++place)
+              {
+                uint16_t *slots = reinterpret_cast<uint16_t *>(wb + warp_head + kWaveChunkBytes * (place / 4));
+                int32_t shared_slot = -1;
+                for (int32_t l = 16 * half; l < 16 * half + 16 && shared_slot < 0; ++l)
+                  if (placed[(32 * w + l) * kMaxPlaces + place])
+                    shared_slot = slots[4 * l + place % 4];
+                if (shared_slot >= 0)
+                  for (int32_t l = 16 * half; l < 16 * half + 16; ++l)
+                    if (!placed[(32 * w + l) * kMaxPlaces + place])
+                      slots[4 * l + place % 4] = (uint16_t)shared_slot;
+              }
         }
       P.max_tile = std::max(P.max_tile, bytes);
 
