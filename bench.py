@@ -431,6 +431,7 @@ def main():
     # ---- per-kernel rooflines (CUDA events on the launch stream, L2 flushed between launches)
     peak, peak_kind = load_peaks()
     kernels = {}
+    fp64_peak_tflops = None
     if not args.no_kernels:
         names = {"spmv_vel": pkg.BENCH_SPMV_VEL, "spmv_pres": pkg.BENCH_SPMV_PRES, "spmv_grad": pkg.BENCH_SPMV_GRAD,
                  "spmv_grad_T": pkg.BENCH_SPMV_GRAD_T, "assemble_advection": pkg.BENCH_ASSEMBLE,
@@ -440,6 +441,15 @@ def main():
             ms, nbytes, nl = ctx.bench_kernel(kid, warmup=3, reps=10, flush_l2=True)
             gbs = nbytes / (ms * 1e-3) / 1e9
             kernels[name] = {"ms": ms, "algorithmic_bytes": nbytes, "GB/s": gbs, "frac": gbs / peak, "launches": nl}
+        # the assembly is FP64-FMA work: 2 (dim + 1) dpc^3 flop per cell against the FMA rate
+        # measured here, now
+        ms, flops, _ = ctx.bench_kernel(pkg.BENCH_FP64_FMA, warmup=2, reps=5, flush_l2=False)
+        fp64_peak_tflops = flops / (ms * 1e-3) / 1e12
+        dpc = 3 ** disc.dim
+        asm_flops = 2.0 * (disc.dim + 1) * dpc ** 3 * disc.n_cells
+        a = kernels["assemble_advection"]
+        a.update({"flops": asm_flops, "TFLOP/s": asm_flops / (a["ms"] * 1e-3) / 1e12,
+                  "frac_fp64": asm_flops / (a["ms"] * 1e-3) / 1e12 / fp64_peak_tflops})
     # the kernel that dominates the step: the ILU(0) substitution sweeps (SpMV is reported beside it)
     roofline = None
     if kernels:
@@ -484,7 +494,7 @@ def main():
             "config": config_dict(args, disc, world),
             "dof_steps_per_s": value * dof, "wall_ms_per_step": 1e3 * wall_s / args.steps,
             "sections_ms_per_step": sections, "gpu_launches": launches, "clocks": clocks, "e2e": e2e, "roofline": roofline,
-            "kernels": kernels, "cpu_baseline": cpu_baseline,
+            "kernels": kernels, "fp64_peak_tflops": fp64_peak_tflops, "cpu_baseline": cpu_baseline,
             "setup_s": {"host_discretisation": disc.info.setup_seconds, "device_context": ctx_seconds},
             # last, so that a truncated tail of the line keeps them
             "iterations": its, "parity": parity,

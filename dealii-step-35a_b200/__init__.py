@@ -27,7 +27,7 @@ U_N, U_N_MINUS_1, U_STAR, FORCE, PRES_N, PRES_N_MINUS_1, PHI_N, PHI_N_MINUS_1, P
 VEL_ADVECTION, VEL_IT_MATRIX, VEL_ILU = range(3)
 # s35_bench_kernel
 (BENCH_SPMV_VEL, BENCH_SPMV_PRES, BENCH_SPMV_GRAD, BENCH_SPMV_GRAD_T, BENCH_ASSEMBLE, BENCH_ILU_APPLY_VEL,
- BENCH_ILU_APPLY_PRES, BENCH_DOT, BENCH_ADD_AND_DOT, BENCH_ILU_FACTOR_VEL) = range(10)
+ BENCH_ILU_APPLY_PRES, BENCH_DOT, BENCH_ADD_AND_DOT, BENCH_ILU_FACTOR_VEL, BENCH_FP64_FMA) = range(11)
 
 SECTIONS = ("interpolate_velocity", "setup_diffusion_rhs", "solve_diffusion_component", "assemble_advection_term",
             "projection_step_setup", "projection_step_solve", "update_pressure")

@@ -94,6 +94,29 @@ struct Staged
 
 } // namespace
 
+namespace {
+// eight independent FMA chains per thread: enough to cover the 8-cycle latency at 8 warps per scheduler
+__global__ void k_fp64_fma(double *out, int iters, int n_out)
+{
+  double a0 = threadIdx.x * 1e-9, a1 = a0 + 1., a2 = a0 + 2., a3 = a0 + 3., a4 = a0 + 4., a5 = a0 + 5., a6 = a0 + 6., a7 = a0 + 7.;
+  const double m = 1.0 - 1e-12, b = 1e-12;
+  for (int k = 0; k < iters; ++k)
+    {
+      a0 = fma(a0, m, b);
+      a1 = fma(a1, m, b);
+      a2 = fma(a2, m, b);
+      a3 = fma(a3, m, b);
+      a4 = fma(a4, m, b);
+      a5 = fma(a5, m, b);
+      a6 = fma(a6, m, b);
+      a7 = fma(a7, m, b);
+    }
+  const double sum = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+  if (sum == 123.456) // never: keeps the chains alive
+    out[(blockIdx.x * blockDim.x + threadIdx.x) % n_out] = sum;
+}
+} // namespace
+
 extern "C" {
 
 const char *s35_last_error(void) { return g_last_error.c_str(); }
@@ -584,6 +607,14 @@ s35_status s35_ctx_bench_kernel(s35_ctx *ctx, s35_bench_kernel kernel, int32_t w
         {
           const double *input = factor_input();
           run = [&c, input, s] { c.prec_vel[0].factor(input, c.diag_strength, s); };
+        }
+        break;
+      case S35_BENCH_FP64_FMA:
+        {
+          // the FP64 FMA rate this GPU sustains: the roof of the assembly ("measure FP64 peak")
+          const int blocks = sm_count() * 8, iters = 4096;
+          bytes = 2.0 * 8.0 * iters * (double)blocks * 256.0; // flops, not bytes
+          run = [&c, blocks, iters, yv, s] { S35_LAUNCH(k_fp64_fma, blocks, 256, 0, s, yv, iters, (int)c.nv); };
         }
         break;
       default: throw Error(S35_ERR_INVALID, "unknown bench kernel");

@@ -311,7 +311,8 @@ typedef enum s35_bench_kernel
   S35_BENCH_ILU_APPLY_PRES = 6,
   S35_BENCH_DOT = 7,
   S35_BENCH_ADD_AND_DOT = 8,
-  S35_BENCH_ILU_FACTOR_VEL = 9
+  S35_BENCH_ILU_FACTOR_VEL = 9,
+  S35_BENCH_FP64_FMA = 10      /* FP64 FMA rate of the device; *algorithmic_bytes returns FLOPS per launch */
 } s35_bench_kernel;
 s35_status s35_ctx_bench_kernel(s35_ctx *ctx, s35_bench_kernel kernel, int32_t warmup, int32_t reps, int flush_l2,
                                 double *avg_ms, double *algorithmic_bytes, int64_t *launches);

@@ -29,8 +29,9 @@ def velocity_scale(orc, pkg, dim):
     return max(np.abs(orc.get_field(pkg.U_N, d)).max() for d in range(dim))
 
 
-def assert_fields_match(pkg, ctx, orc, dim, tol=TOL):
-    """max-norm and l2-norm differences relative to the field norm (velocity: the norm of the whole vector field)."""
+def assert_fields_match(pkg, ctx, orc, dim, tol=TOL, phi_tol=None):
+    """max-norm and l2-norm differences relative to the field norm (velocity: the norm of the whole vector field).
+    phi_tol: a tolerance of its own for the pressure increments phi_n, phi_n_minus_1."""
     for f in (pkg.U_N, pkg.U_N_MINUS_1):
         a = np.concatenate([ctx.get_field(f, d) for d in range(dim)])
         b = np.concatenate([orc.get_field(f, d) for d in range(dim)])
@@ -38,8 +39,9 @@ def assert_fields_match(pkg, ctx, orc, dim, tol=TOL):
         assert np.linalg.norm(a - b) <= tol * np.linalg.norm(b)
     for f in (pkg.PRES_N, pkg.PRES_N_MINUS_1, pkg.PHI_N, pkg.PHI_N_MINUS_1):
         a, b = ctx.get_field(f), orc.get_field(f)
-        assert rel_diff(a, b) < tol
-        assert np.linalg.norm(a - b) <= tol * np.linalg.norm(b)
+        t = phi_tol if phi_tol is not None and f in (pkg.PHI_N, pkg.PHI_N_MINUS_1) else tol
+        assert rel_diff(a, b) < t
+        assert np.linalg.norm(a - b) <= t * np.linalg.norm(b)
 
 
 @pytest.mark.parametrize("mesh,dim,refines", [("nsbench2.s35m", 2, 0), ("nsbench2.s35m", 2, 2), ("cylinder3d.s35m", 3, 0)])
@@ -115,6 +117,31 @@ def test_time_steps_match_oracle(pkg, ob, make_disc, mesh, dim, refines, steps, 
     cd_dev = disc.drag_lift(reynolds, u_dev, ctx.get_field(pkg.PRES_N))
     cd_ref = disc.drag_lift(reynolds, u_ref, orc.get_field(pkg.PRES_N))
     assert np.abs(cd_dev - cd_ref).max() <= 1e-6 * max(1.0, np.abs(cd_ref).max())
+
+
+def test_config_1_all_hundred_steps_on_the_device(pkg, ob, make_disc):
+    """BASELINE.json config 1 over its whole run (nsbench2.inp, Re = 100, T = 0.0505: steps n = 2 .. 101): u and p to
+    1e-8 (phi to 1e-7), drag / lift to 1e-6 against the oracle every 25 steps, iteration counts within one, and the pressure-mass
+    solve of update_pressure (CG in place of the reference's direct solve) below 1e-12 ||rhs|| in every checked step."""
+    disc = make_disc("nsbench2.s35m", 2, final_time=0.0505)
+    ctx, orc = make_pair(pkg, ob, disc)
+    for first in range(2, 102, 25):
+        ctx.advance(first, 25)
+        orc.advance(first, 25)
+        # u and p to 1e-8.  phi is the solution of a Poisson problem stopped at eps * ||rhs||; once the start-up has
+        # decayed it is two orders smaller than p, and its own relative error is eps x condition number (measured: 3e-8
+        # in the l2 norm after 25 steps): 1e-7, stated in BASELINE.md section 4.
+        assert_fields_match(pkg, ctx, orc, 2, phi_tol=1e-7)
+        for d in range(2):
+            assert abs(ctx.solver_stats(d).iterations - orc.solver_stats(d).iterations) <= 1
+        assert abs(ctx.solver_stats(-1).iterations - orc.solver_stats(-1).iterations) <= 1
+        u_d = np.concatenate([ctx.get_field(pkg.U_N, d) for d in range(2)])
+        u_o = np.concatenate([orc.get_field(pkg.U_N, d) for d in range(2)])
+        cd_d = disc.drag_lift(100.0, u_d, ctx.get_field(pkg.PRES_N))
+        cd_o = disc.drag_lift(100.0, u_o, orc.get_field(pkg.PRES_N))
+        assert np.abs(cd_d - cd_o).max() <= 1e-6 * max(1.0, np.abs(cd_o).max())
+        mass = ctx.solver_stats(-2)
+        assert 0 < mass.iterations <= 200 and mass.final_residual <= 1e-12 * mass.initial_residual
 
 
 def test_benchmarked_workload_first_step_matches_oracle(pkg, make_disc):
