@@ -592,6 +592,30 @@ bool wave_create(DevIlu &p, const DevMatrix &A, cudaStream_t s, bool force = fal
     }
   if (!force && (double)(F.far_entries + B.far_entries) > 0.02 * (double)(F.entries + B.entries + 1))
     return false; // too many values outside the window: every one is a trip to L2 in the middle of a tile
+  // Levels narrower than a warp on average (coarse meshes, BASELINE configs 2 and 3: ~16 rows per level): five groups of
+  // ONE warp hand the levels round (measured, tools/tune_ilu.py narrow: 8-17 % faster sweeps than 3 x 256 threads, of which
+  // most would idle and still take part in every barrier).
+  const double rows_per_level = (double)n / std::max(1, std::max(F.n_levels, B.n_levels));
+  if (rows_per_level <= 24.0 && !std::getenv("S35_WAVE_GROUPS") && !std::getenv("S35_WAVE_GROUP_ROWS"))
+    {
+      WavefrontOptions narrow = opt;
+      narrow.groups = 5;
+      narrow.group_rows = 32;
+      try
+        {
+          WavefrontPlan B2 = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), false, nullptr, narrow);
+          WavefrontPlan F2 = wavefront_pack(n, A.h_rowptr.data(), A.h_col.data(), diag.data(), true, B2.rhs_slot.data(), narrow);
+          if (force || (double)(F2.far_entries + B2.far_entries) <= 0.02 * (double)(F2.entries + B2.entries + 1))
+            {
+              B = std::move(B2);
+              F = std::move(F2);
+              opt = narrow;
+            }
+        }
+      catch (const std::invalid_argument &)
+        {
+        }
+    }
   w.groups = opt.groups;
   w.group_rows = opt.group_rows;
   w.window = opt.window;

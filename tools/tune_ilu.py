@@ -36,6 +36,9 @@ VARIANT_SETS = {
     "wavefront": [{"S35_ILU_MODE": "wide"}, {}]
                  + [{"S35_WAVE_GROUPS": str(g), "S35_WAVE_GROUP_ROWS": str(w)} for g, w in ((2, 256), (4, 192), (6, 128))]
                  + [{"S35_WAVE_RING_KB": "112"}, {"S35_WAVE_WINDOW": "4096", "S35_WAVE_RING_KB": "176"}],
+    # small factors: levels of ~16 rows; few warps keep the load queues short
+    "narrow": [{}] + [{"S35_WAVE_GROUPS": str(g), "S35_WAVE_GROUP_ROWS": str(w)}
+                      for g, w in ((3, 32), (5, 32), (7, 32), (3, 64), (5, 64), (3, 128), (5, 128))],
 }
 
 
