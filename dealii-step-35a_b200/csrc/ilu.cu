@@ -593,7 +593,7 @@ bool wave_create(DevIlu &p, const DevMatrix &A, cudaStream_t s, bool force = fal
   if (!force && (double)(F.far_entries + B.far_entries) > 0.02 * (double)(F.entries + B.entries + 1))
     return false; // too many values outside the window: every one is a trip to L2 in the middle of a tile
   // Levels narrower than a warp on average (coarse meshes, BASELINE configs 2 and 3: ~16 rows per level): five groups of
-  // ONE warp hand the levels round (measured, tools/tune_ilu.py narrow: 8-17 % faster sweeps than 3 x 256 threads, of which
+  // ONE warp hand the levels round (measured, tools/tune_ilu.py narrow: 8-17 % faster sweeps than the default shape, of which
   // most would idle and still take part in every barrier).
   const double rows_per_level = (double)n / std::max(1, std::max(F.n_levels, B.n_levels));
   if (rows_per_level <= 24.0 && !std::getenv("S35_WAVE_GROUPS") && !std::getenv("S35_WAVE_GROUP_ROWS"))

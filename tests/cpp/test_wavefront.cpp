@@ -163,7 +163,7 @@ int check(const char *name, const Csr &A, const s35::WavefrontOptions &opt, std:
           const int32_t *d = P->directory.data() + 4 * (size_t)t;
             const int32_t rows = reinterpret_cast<const int32_t *>(P->blob.data() + (size_t)d[0] * 16)[1];
           const int32_t *rd = P->rhs_dir.data() + 2 * (size_t)t;
-          if (rows < 1 || rows > opt.group_rows || d[2] > opt.max_tile_bytes || d[2] % 128 || d[0] % 8 || d[1] % 8 || rd[1] % 128 ||
+          if (rows < 1 || rows > opt.group_rows || d[2] + rd[1] > opt.ring_bytes / 2 || d[2] % 128 || d[0] % 8 || d[1] % 8 || rd[1] % 128 ||
               rd[0] % 16 || rd[1] < 8 * rows || d[1] * 16 + d[2] + rd[1] > opt.ring_bytes || d[3] >= t || d[3] < t - opt.slots)
             bad |= 8;
         }
@@ -186,10 +186,62 @@ std::vector<int32_t> identity(int32_t n)
 
 } // namespace
 
-int main()
+// a pattern written by the Python test (int32: n, nnz, rowptr[n + 1], col[nnz]): the matrices of a real mesh
+Csr read_pattern(const char *file, std::mt19937 &rng)
+{
+  Csr A;
+  FILE *f = std::fopen(file, "rb");
+  int32_t head[2] = {0, 0};
+  if (!f || std::fread(head, 4, 2, f) != 2)
+    throw std::runtime_error("cannot read the pattern file");
+  A.n = head[0];
+  A.rowptr.resize(A.n + 1);
+  A.col.resize(head[1]);
+  if (std::fread(A.rowptr.data(), 4, A.rowptr.size(), f) != A.rowptr.size() || std::fread(A.col.data(), 4, A.col.size(), f) != A.col.size())
+    throw std::runtime_error("short pattern file");
+  std::fclose(f);
+  A.diag.assign(A.n, -1);
+  A.val.resize(A.col.size());
+  std::uniform_real_distribution<double> u(-1.0, 1.0);
+  for (int32_t r = 0; r < A.n; ++r)
+    {
+      const int32_t len = A.rowptr[r + 1] - A.rowptr[r];
+      for (int32_t k = A.rowptr[r]; k < A.rowptr[r + 1]; ++k)
+        {
+          if (A.col[k] == r)
+            A.diag[r] = k;
+          A.val[k] = A.col[k] == r ? 1.0 / (1.0 + 0.1 * u(rng)) : u(rng) / (2.0 * len); // inverse pivots near 1, small couplings
+        }
+    }
+  return A;
+}
+
+int main(int argc, char **argv)
 {
   std::mt19937 rng(35);
   int bad = 0;
+  if (argc > 1)
+    {
+      // the shapes the library chooses: the default, and five one-warp groups for narrow levels
+      s35::WavefrontOptions standard, narrow;
+      narrow.groups = 5;
+      narrow.group_rows = 32;
+      for (int k = 1; k < argc; ++k)
+        {
+          const Csr A = read_pattern(argv[k], rng);
+          for (const s35::WavefrontOptions *o : {&standard, &narrow})
+            try
+              {
+                bad |= check(argv[k], A, *o, rng);
+              }
+            catch (const std::invalid_argument &e) // "not for this sweep" is an answer; a logic_error is a fault
+              {
+                std::printf("  %s: declined (%s)\n", argv[k], e.what());
+              }
+        }
+      std::printf(bad ? "wavefront: FAILED (%d)\n" : "wavefront: all schedules reproduce the substitutions\n", bad);
+      return bad ? 1 : 0;
+    }
   s35::WavefrontOptions standard, tiny_window, tiny_tiles, two_groups;
   tiny_window.window = 256; // = (groups + 1) * group_rows: every older value is far
   tiny_window.ring_bytes = 64 * 1024;

@@ -28,3 +28,26 @@ def test_wavefront_schedule_reproduces_the_substitutions(tmp_path):
     r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "all schedules reproduce the substitutions" in r.stdout
+
+
+def test_wavefront_schedule_on_the_matrices_of_the_meshes(tmp_path, pkg, make_disc):
+    """The patterns the library really packs (pressure Laplace, velocity mass / iteration matrix of the 2-D and 3-D coarse
+    meshes), in the two shapes it chooses.  Long Q2 rows make a warp's old and fresh runs come from different rows: the
+    case in which a tile grows beyond its planned size."""
+    import numpy as np
+    exe = str(tmp_path / "test_wavefront")
+    env = dict(os.environ)
+    env.pop("CXX", None)
+    subprocess.run(["g++", "-std=c++17", "-O2", "-I", os.path.join(ROOT, "dealii-step-35a_b200", "csrc"),
+                    os.path.join(ROOT, "tests", "cpp", "test_wavefront.cpp"), "-o", exe], check=True, env=env)
+    files = []
+    for mesh, dim in (("nsbench2.s35m", 2), ("cylinder3d.s35m", 3)):
+        disc = make_disc(mesh, dim)
+        for which in ("plap", "velm", "velc"):
+            rp, cl, _ = disc.csr(which)
+            f = str(tmp_path / ("%s_%s.bin" % (mesh.split(".")[0], which)))
+            np.concatenate([np.array([len(rp) - 1, len(cl)], np.int32), rp.astype(np.int32), cl.astype(np.int32)]).tofile(f)
+            files.append(f)
+    r = subprocess.run([exe] + files, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "all schedules reproduce the substitutions" in r.stdout
