@@ -201,6 +201,8 @@ bool cg_graph_enabled()
 
 CgSolver::~CgSolver()
 {
+  if (res_copied)
+    cudaEventDestroy(res_copied);
   for (LoopGraph &l : loops)
     {
       if (l.exec)
@@ -351,15 +353,21 @@ bool CgSolver::solve(const DevMatrix &P, const double *values, DevIlu *prec, dou
           scalar_divide(sc + ALPHA, sc + GH, sc + DH, nullptr, s);
           vec_cg_update(sc + RES, x, g, DScal(sc + ALPHA), d, h, n, dist.local_post(true), ws, s);
           dist.finish_sums(sc + RES, 1, true, s);
-          res = read_res();
-          state = solver_check(it, res, tol, max_iterations);
-          if (state != SolverState::iterate)
-            break;
+          // The rest of the iteration touches only h, gh, beta and d -- not x, not g -- so it is launched before the
+          // host has seen the residual: the wait for the copy and the next launches overlap with the preconditioner
+          // instead of leaving the GPU idle.  If this was the last iteration, one application was for nothing.
+          if (!res_copied)
+            S35_CUDA(cudaEventCreateWithFlags(&res_copied, cudaEventDisableTiming));
+          S35_CUDA(cudaMemcpyAsync(res_host.ptr, sc + RES, sizeof(double), cudaMemcpyDeviceToHost, s));
+          S35_CUDA(cudaEventRecord(res_copied, s));
           precondition(h, g);
           dot(sc + GHNEW, g, h);
           // beta = gh_new / gh_old ; gh = gh_new
           scalar_divide(sc + BETA, sc + GHNEW, sc + GH, sc + GH, s);
           vec_lincomb(d, DScal(sc + BETA), d, DScal(-1.0), h, n, s);
+          S35_CUDA(cudaEventSynchronize(res_copied));
+          res = res_host.ptr[0];
+          state = solver_check(it, res, tol, max_iterations);
         }
     }
   stats.iterations = it;

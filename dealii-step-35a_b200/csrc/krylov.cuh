@@ -84,6 +84,7 @@ struct CgSolver
   DevBuf<double> g, d, h;
   DevBuf<double> scal;    // [0] d.h  [1] alpha  [2] gh  [3] res  [4] gh_new  [5] beta  [6] tol  [7] max its  [8] it  [9] state
   PinnedBuf<double> res_host;
+  cudaEvent_t res_copied = nullptr; // host-driven loop: the residual of the iteration has reached res_host
   ReduceWs ws;
   cudaStream_t stream = 0;
   DistLink dist;
