@@ -187,6 +187,9 @@ typedef struct s35_problem
   double dt, reynolds;
   double vel_eps, vel_diag_strength;
   int32_t vel_max_iterations, vel_krylov_size, vel_off_diagonals, vel_update_prec;
+  /* vel_off_diagonals = k > 0 (SparseILU::AdditionalData::extra_off_diagonals, step-35a.cc:1070-1074, 1312-1319): both
+   * ILU factors live on the matrix pattern plus the entries (r, r - k .. r + k).  One GPU only; not with ilu_blocks.
+   * s35_ctx_get_operator_values(S35_VEL_ILU) then returns the factor's entries at the matrix's own positions. */
   int32_t rotational;         /* METHOD_ROTATIONAL = 1, METHOD_STANDARD = 0 */
 
   /* GATED ALTERNATIVE, not the reference's preconditioner.  0 or 1: ILU(0) of the whole matrix, exactly what
